@@ -1,0 +1,343 @@
+// extern "C" entry points of libbgr.so (include/bgr.h) and the host-side orchestration of the
+// forward / backward passes (replaces reference rasterizer_impl.cu:198-434).
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+
+#include "../../include/bgr.h"
+#include "bgr_common.cuh"
+
+namespace {
+
+thread_local std::string g_last_error;
+
+int fail(int code, const std::string& msg)
+{
+    g_last_error = msg;
+    return code;
+}
+
+int check_cuda(cudaError_t e, const char* what)
+{
+    if (e == cudaSuccess) return BGR_OK;
+    return fail(BGR_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+
+// debug mode: synchronise and surface kernel faults with the stage name (auxiliary.h:166-173)
+int stage_check(bool debug, cudaStream_t s, const char* stage)
+{
+    cudaError_t e = cudaPeekAtLastError();
+    if (e == cudaSuccess && debug) e = cudaStreamSynchronize(s);
+    if (e == cudaSuccess && debug) e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        std::fprintf(stderr, "\n[CUDA ERROR] in bgr stage '%s': %s\n", stage, cudaGetErrorString(e));
+        return fail(BGR_ERR_CUDA, std::string("stage '") + stage + "': " + cudaGetErrorString(e));
+    }
+    return BGR_OK;
+}
+
+bgr::GeomControl* pinned_control()
+{
+    thread_local bgr::GeomControl* host = nullptr;
+    if (host == nullptr) {
+        if (cudaMallocHost(reinterpret_cast<void**>(&host), sizeof(bgr::GeomControl)) != cudaSuccess)
+            host = nullptr;
+    }
+    return host;
+}
+
+bool env_flag(const char* name)
+{
+    const char* v = std::getenv(name);
+    return v != nullptr && v[0] != '\0' && v[0] != '0';
+}
+
+}  // namespace
+
+extern "C" {
+
+BGR_API const char* bgr_last_error(void) { return g_last_error.c_str(); }
+BGR_API const char* bgr_version(void) { return "bgr 0.1 (sm_100a)"; }
+
+BGR_API size_t bgr_geom_bytes(int P) { return bgr::geom_layout((size_t)std::max(P, 0)).total; }
+BGR_API size_t bgr_image_bytes(int width, int height)
+{
+    return bgr::image_layout((size_t)std::max(width, 0), (size_t)std::max(height, 0)).total;
+}
+BGR_API size_t bgr_binning_bytes(int R) { return bgr::binning_layout((size_t)std::max(R, 0)).total; }
+BGR_API size_t bgr_backward_scratch_bytes(int P)
+{
+    return bgr::align_up((size_t)std::max(P, 0) * bgr::ACC_STRIDE * sizeof(float), 256);
+}
+
+BGR_API void bgr_geom_layout(int P, size_t* o)
+{
+    const bgr::GeomLayout L = bgr::geom_layout((size_t)P);
+    o[0] = L.rec; o[1] = L.tiles; o[2] = L.offsets; o[3] = L.control;
+}
+BGR_API void bgr_image_layout(int width, int height, size_t* o)
+{
+    const bgr::ImageLayout L = bgr::image_layout((size_t)width, (size_t)height);
+    o[0] = L.final_T; o[1] = L.n_contrib; o[2] = L.ranges;
+}
+BGR_API void bgr_binning_layout(int R, size_t* o)
+{
+    const bgr::BinningLayout L = bgr::binning_layout((size_t)R);
+    o[0] = L.point_list; o[1] = L.keys_a; o[2] = L.keys_b; o[3] = L.vals_a; o[4] = L.vals_b;
+    o[5] = L.sort_temp;
+}
+
+BGR_API int bgr_forward(const BgrForwardArgs* a, bgr_alloc_fn geom_alloc, void* geom_user,
+                bgr_alloc_fn binning_alloc, void* binning_user, bgr_alloc_fn image_alloc,
+                void* image_user, void* stream_v, int* num_rendered)
+{
+    using namespace bgr;
+    cudaStream_t s = static_cast<cudaStream_t>(stream_v);
+    if (a == nullptr || num_rendered == nullptr) return fail(BGR_ERR_INVALID_ARG, "null argument");
+    *num_rendered = 0;
+    if (a->P < 0 || a->width <= 0 || a->height <= 0)
+        return fail(BGR_ERR_INVALID_ARG, "P must be >= 0 and the image non-empty");
+    const bool debug = a->debug != 0;
+    const size_t npix = (size_t)a->width * a->height;
+
+    if (a->P == 0) {
+        // the reference skips the core entirely: the image stays zero, NOT background
+        // (rasterize_points.cu:81)
+        int rc = check_cuda(cudaMemsetAsync(a->out_color, 0, 3 * npix * sizeof(float), s), "memset");
+        return rc;
+    }
+    if (a->means3D == nullptr || a->opacities == nullptr || a->viewmatrix == nullptr ||
+        a->projmatrix == nullptr || a->cam_pos == nullptr || a->background == nullptr ||
+        a->out_color == nullptr || a->radii == nullptr)
+        return fail(BGR_ERR_INVALID_ARG, "required pointer is NULL");
+    if (a->shs == nullptr && a->colors_precomp == nullptr)
+        return fail(BGR_ERR_INVALID_ARG, "provide SHs or precomputed colours");
+    if (a->cov3D_precomp == nullptr && (a->scales == nullptr || a->rotations == nullptr))
+        return fail(BGR_ERR_INVALID_ARG, "provide scales+rotations or a precomputed 3D covariance");
+    if (a->shs != nullptr && a->colors_precomp == nullptr &&
+        (a->D < 0 || a->D > 3 || (a->D + 1) * (a->D + 1) > a->M))
+        return fail(BGR_ERR_INVALID_ARG, "SH degree does not fit the coefficient count");
+
+    const int grid_x = (a->width + TILE_X - 1) / TILE_X;
+    const int grid_y = (a->height + TILE_Y - 1) / TILE_Y;
+    const uint32_t num_tiles = (uint32_t)grid_x * (uint32_t)grid_y;
+    const float focal_y = a->height / (2.0f * a->tan_fovy);
+    const float focal_x = a->width / (2.0f * a->tan_fovx);
+
+    const GeomLayout GL = geom_layout((size_t)a->P);
+    const ImageLayout IL = image_layout((size_t)a->width, (size_t)a->height);
+    unsigned char* geom = static_cast<unsigned char*>(geom_alloc(GL.total, geom_user));
+    unsigned char* img = static_cast<unsigned char*>(image_alloc(IL.total, image_user));
+    if (geom == nullptr || img == nullptr) return fail(BGR_ERR_ALLOC, "scratch allocation failed");
+
+    GaussRec* rec = reinterpret_cast<GaussRec*>(geom + GL.rec);
+    uint32_t* tiles = reinterpret_cast<uint32_t*>(geom + GL.tiles);
+    uint32_t* offsets = reinterpret_cast<uint32_t*>(geom + GL.offsets);
+    GeomControl* ctl = reinterpret_cast<GeomControl*>(geom + GL.control);
+    uint64_t* scan_state = reinterpret_cast<uint64_t*>(geom + GL.scan_state);
+    float* final_T = reinterpret_cast<float*>(img + IL.final_T);
+    uint32_t* n_contrib = reinterpret_cast<uint32_t*>(img + IL.n_contrib);
+    uint2* ranges = reinterpret_cast<uint2*>(img + IL.ranges);
+
+    int rc;
+    // control block (counters, depth range stored as max(~bits)/max(bits)) + scan look-back state
+    if ((rc = check_cuda(cudaMemsetAsync(ctl, 0, GL.total - GL.control, s), "memset control")))
+        return rc;
+
+    PreprocessParams pp;
+    pp.P = a->P; pp.D = a->D; pp.M = a->M; pp.W = a->width; pp.H = a->height;
+    pp.means3D = a->means3D; pp.scales = a->scales; pp.scale_modifier = a->scale_modifier;
+    pp.rotations = a->rotations; pp.opacities = a->opacities; pp.shs = a->shs;
+    pp.cov3D_precomp = a->cov3D_precomp; pp.colors_precomp = a->colors_precomp;
+    pp.viewmatrix = a->viewmatrix; pp.projmatrix = a->projmatrix; pp.cam_pos = a->cam_pos;
+    pp.tan_fovx = a->tan_fovx; pp.tan_fovy = a->tan_fovy; pp.focal_x = focal_x; pp.focal_y = focal_y;
+    pp.grid_x = grid_x; pp.grid_y = grid_y; pp.prefiltered = a->prefiltered;
+    pp.radii = a->radii; pp.rec = rec; pp.tiles_touched = tiles; pp.control = ctl;
+    launch_preprocess(pp, s);
+    if ((rc = stage_check(debug, s, "preprocess"))) return rc;
+
+    launch_inclusive_scan(tiles, offsets, (size_t)a->P, scan_state, &ctl->scan_ticket,
+                          &ctl->num_rendered, s);
+    if ((rc = stage_check(debug, s, "scan"))) return rc;
+
+    GeomControl* host = pinned_control();
+    if (host == nullptr) return fail(BGR_ERR_CUDA, "pinned host allocation failed");
+    if ((rc = check_cuda(cudaMemcpyAsync(host, ctl, sizeof(GeomControl), cudaMemcpyDeviceToHost, s),
+                         "read back num_rendered")))
+        return rc;
+    if ((rc = check_cuda(cudaStreamSynchronize(s), "sync after scan"))) return rc;
+
+    const uint32_t R = host->num_rendered;
+    if (R >= (1u << 30))
+        return fail(BGR_ERR_OVERFLOW, "num_rendered >= 2^30 tile instances is not supported");
+
+    const BinningLayout BL = binning_layout((size_t)R);
+    unsigned char* bin = static_cast<unsigned char*>(binning_alloc(BL.total, binning_user));
+    if (bin == nullptr) return fail(BGR_ERR_ALLOC, "binning allocation failed");
+    uint32_t* point_list = reinterpret_cast<uint32_t*>(bin + BL.point_list);
+
+    if (R > 0) {
+        KeyFormat kf;
+        kf.depth_min = ~host->depth_min_bits;  // stored inverted so that zero-init works
+        const uint32_t depth_max = host->depth_max_bits;
+        kf.nb_idx = bits_for((uint64_t)(a->P - 1));
+        kf.nb_depth = bits_for((uint64_t)(depth_max - kf.depth_min));
+        kf.nb_tile = bits_for((uint64_t)(num_tiles - 1));
+        kf.pairs = (kf.nb_idx + kf.nb_depth + kf.nb_tile > 64 || env_flag("BGR_FORCE_PAIRS")) ? 1 : 0;
+        if (kf.pairs) {
+            kf.sort_lo = 0;
+            kf.sort_hi = kf.nb_depth + kf.nb_tile;
+            kf.tile_shift = kf.nb_depth;
+        } else {
+            kf.sort_lo = kf.nb_idx;
+            kf.sort_hi = kf.nb_idx + kf.nb_depth + kf.nb_tile;
+            kf.tile_shift = kf.nb_idx + kf.nb_depth;
+        }
+        uint64_t* keys_a = reinterpret_cast<uint64_t*>(bin + BL.keys_a);
+        uint64_t* keys_b = reinterpret_cast<uint64_t*>(bin + BL.keys_b);
+        uint32_t* vals_a = kf.pairs ? reinterpret_cast<uint32_t*>(bin + BL.vals_a) : nullptr;
+        uint32_t* vals_b = kf.pairs ? reinterpret_cast<uint32_t*>(bin + BL.vals_b) : nullptr;
+        // emit into the buffer from which an odd/even number of passes ends in keys_a
+        const int npasses = radix_sort_passes(kf.sort_lo, kf.sort_hi);
+        const bool start_in_b = (npasses & 1) != 0;
+        uint64_t* k_in = start_in_b ? keys_b : keys_a;
+        uint64_t* k_alt = start_in_b ? keys_a : keys_b;
+        uint32_t* v_in = start_in_b ? vals_b : vals_a;
+        uint32_t* v_alt = start_in_b ? vals_a : vals_b;
+
+        launch_emit_keys(a->P, rec, offsets, a->radii, grid_x, grid_y, kf, k_in, v_in, s);
+        if ((rc = stage_check(debug, s, "emit keys"))) return rc;
+
+        int in_alt = 0;
+        if (radix_sort(k_in, k_alt, v_in, v_alt, (size_t)R, kf.sort_lo, kf.sort_hi,
+                       bin + BL.sort_temp, s, &in_alt) != 0)
+            return fail(BGR_ERR_INVALID_ARG, "radix sort configuration rejected");
+        if ((rc = stage_check(debug, s, "radix sort"))) return rc;
+        const uint64_t* k_sorted = in_alt ? k_alt : k_in;  // == keys_a by construction
+        const uint32_t* v_sorted = in_alt ? v_alt : v_in;
+
+        launch_tile_ranges((size_t)R, k_sorted, v_sorted, kf, num_tiles, ranges, point_list, s);
+        if ((rc = stage_check(debug, s, "tile ranges"))) return rc;
+    } else {
+        if ((rc = check_cuda(cudaMemsetAsync(ranges, 0, (size_t)num_tiles * sizeof(uint2), s),
+                             "memset ranges")))
+            return rc;
+    }
+
+    launch_render_forward(a->width, a->height, ranges, point_list, rec, nullptr, a->background,
+                          final_T, n_contrib, a->out_color, s);
+    if ((rc = stage_check(debug, s, "render forward"))) return rc;
+
+    *num_rendered = (int)R;
+    return BGR_OK;
+}
+
+BGR_API int bgr_backward(const BgrBackwardArgs* a, void* stream_v)
+{
+    using namespace bgr;
+    cudaStream_t s = static_cast<cudaStream_t>(stream_v);
+    if (a == nullptr) return fail(BGR_ERR_INVALID_ARG, "null argument");
+    if (a->P < 0 || a->width <= 0 || a->height <= 0 || a->R < 0)
+        return fail(BGR_ERR_INVALID_ARG, "bad sizes");
+    if (a->P == 0) return BGR_OK;
+    if (a->geom_buffer == nullptr || a->image_buffer == nullptr || a->scratch == nullptr ||
+        a->dL_dpix == nullptr || a->radii == nullptr || a->means3D == nullptr)
+        return fail(BGR_ERR_INVALID_ARG, "required pointer is NULL");
+    if (a->R > 0 && a->binning_buffer == nullptr)
+        return fail(BGR_ERR_INVALID_ARG, "binning buffer is NULL");
+    const bool debug = a->debug != 0;
+
+    const GeomLayout GL = geom_layout((size_t)a->P);
+    const ImageLayout IL = image_layout((size_t)a->width, (size_t)a->height);
+    const BinningLayout BL = binning_layout((size_t)a->R);
+    const unsigned char* geom = static_cast<const unsigned char*>(a->geom_buffer);
+    const unsigned char* img = static_cast<const unsigned char*>(a->image_buffer);
+    const unsigned char* bin = static_cast<const unsigned char*>(a->binning_buffer);
+    const GaussRec* rec = reinterpret_cast<const GaussRec*>(geom + GL.rec);
+    const float* final_T = reinterpret_cast<const float*>(img + IL.final_T);
+    const uint32_t* n_contrib = reinterpret_cast<const uint32_t*>(img + IL.n_contrib);
+    const uint2* ranges = reinterpret_cast<const uint2*>(img + IL.ranges);
+    float* acc = static_cast<float*>(a->scratch);
+
+    int rc;
+    if ((rc = check_cuda(cudaMemsetAsync(acc, 0, (size_t)a->P * ACC_STRIDE * sizeof(float), s),
+                         "memset accumulators")))
+        return rc;
+
+    if (a->R > 0) {
+        const uint32_t* point_list = reinterpret_cast<const uint32_t*>(bin + BL.point_list);
+        launch_render_backward(a->width, a->height, ranges, point_list, rec, nullptr, a->background,
+                               final_T, n_contrib, a->dL_dpix, acc, s);
+        if ((rc = stage_check(debug, s, "render backward"))) return rc;
+    }
+
+    PreprocessBackwardParams pb;
+    pb.P = a->P; pb.D = a->D; pb.M = a->M; pb.W = a->width; pb.H = a->height;
+    pb.means3D = a->means3D; pb.radii = a->radii; pb.shs = a->shs; pb.scales = a->scales;
+    pb.rotations = a->rotations; pb.scale_modifier = a->scale_modifier;
+    pb.cov3D_precomp = a->cov3D_precomp; pb.colors_precomp = a->colors_precomp;
+    pb.viewmatrix = a->viewmatrix; pb.projmatrix = a->projmatrix; pb.cam_pos = a->cam_pos;
+    pb.focal_y = a->height / (2.0f * a->tan_fovy);
+    pb.focal_x = a->width / (2.0f * a->tan_fovx);
+    pb.tan_fovx = a->tan_fovx; pb.tan_fovy = a->tan_fovy;
+    pb.rec = rec; pb.acc = acc;
+    pb.dL_dmean2D = a->dL_dmean2D; pb.dL_dcolor = a->dL_dcolor; pb.dL_dopacity = a->dL_dopacity;
+    pb.dL_dmean3D = a->dL_dmean3D; pb.dL_dcov3D = a->dL_dcov3D; pb.dL_dsh = a->dL_dsh;
+    pb.dL_dscale = a->dL_dscale; pb.dL_drot = a->dL_drot;
+    if (pb.shs != nullptr && pb.dL_dsh == nullptr)
+        return fail(BGR_ERR_INVALID_ARG, "dL_dsh is NULL although SHs were given");
+    launch_preprocess_backward(pb, s);
+    if ((rc = stage_check(debug, s, "preprocess backward"))) return rc;
+    return BGR_OK;
+}
+
+BGR_API int bgr_mark_visible(int P, const float* means3D, const float* viewmatrix,
+                     const float* /*projmatrix*/, uint8_t* present, void* stream_v)
+{
+    cudaStream_t s = static_cast<cudaStream_t>(stream_v);
+    if (P < 0) return fail(BGR_ERR_INVALID_ARG, "P < 0");
+    if (P == 0) return BGR_OK;
+    if (means3D == nullptr || viewmatrix == nullptr || present == nullptr)
+        return fail(BGR_ERR_INVALID_ARG, "required pointer is NULL");
+    bgr::launch_mark_visible(P, means3D, viewmatrix, present, s);
+    return stage_check(false, s, "mark visible");
+}
+
+BGR_API size_t bgr_sort_temp_bytes(size_t n) { return bgr::sort_temp_layout(n).total; }
+
+BGR_API int bgr_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, size_t n,
+                   int bit_lo, int bit_hi, void* temp, void* stream_v, int* result_in_b)
+{
+    cudaStream_t s = static_cast<cudaStream_t>(stream_v);
+    if (result_in_b == nullptr) return fail(BGR_ERR_INVALID_ARG, "null argument");
+    if (bit_lo < 0 || bit_hi > 64 || bit_hi < bit_lo) return fail(BGR_ERR_INVALID_ARG, "bad bit range");
+    if ((vals_a == nullptr) != (vals_b == nullptr))
+        return fail(BGR_ERR_INVALID_ARG, "give both value buffers or neither");
+    if (bgr::radix_sort(keys_a, keys_b, vals_a, vals_b, n, bit_lo, bit_hi, temp, s, result_in_b) != 0)
+        return fail(BGR_ERR_INVALID_ARG, "unsupported sort size or bit range");
+    return stage_check(false, s, "radix sort");
+}
+
+BGR_API size_t bgr_scan_temp_bytes(size_t n)
+{
+    return bgr::align_up(((n + bgr::SCAN_TILE - 1) / bgr::SCAN_TILE + 1) * 8 + 256, 256);
+}
+
+BGR_API int bgr_inclusive_scan_u32(const uint32_t* in, uint32_t* out, size_t n, void* temp, void* stream_v)
+{
+    cudaStream_t s = static_cast<cudaStream_t>(stream_v);
+    if (n == 0) return BGR_OK;
+    if (n >= (1ull << 32)) return fail(BGR_ERR_INVALID_ARG, "n too large");
+    const size_t bytes = bgr_scan_temp_bytes(n);
+    int rc = check_cuda(cudaMemsetAsync(temp, 0, bytes, s), "memset scan state");
+    if (rc) return rc;
+    // layout: [0,256) ticket, then the look-back state
+    uint32_t* ticket = static_cast<uint32_t*>(temp);
+    uint64_t* state = reinterpret_cast<uint64_t*>(static_cast<unsigned char*>(temp) + 256);
+    bgr::launch_inclusive_scan(in, out, n, state, ticket, nullptr, s);
+    return stage_check(false, s, "scan");
+}
+
+}  // extern "C"

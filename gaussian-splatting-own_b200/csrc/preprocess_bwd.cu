@@ -1,0 +1,345 @@
+// Backward of the per-Gaussian preprocess: K6 (conic -> 3D covariance / mean) and K7 (screen
+// mean -> 3D mean, colour -> SH, 3D covariance -> scale / rotation) fused into ONE pass that also
+// writes the rows of culled Gaussians as zeros, so no output needs a prior memset (the reference
+// zero-fills 300 B/Gaussian per backward, rasterize_points.cu:151-159).
+//
+// Spec: SURVEY.md App. A.9 / A.10 (reference backward.cu:144-396, auxiliary.h:107-117).
+// Tolerance-level parity (gradients); the forward quantities it recomputes (view-space mean,
+// Jacobian, 3D covariance) use the same helpers as the forward preprocess.
+#include "bgr_common.cuh"
+#include "gs_math.cuh"
+
+namespace bgr {
+
+namespace {
+
+constexpr int PB_THREADS = 256;
+
+__device__ __forceinline__ void store3(float* p, float a, float b, float c)
+{
+    p[0] = a; p[1] = b; p[2] = c;
+}
+
+template <bool kVecSH>
+__global__ void __launch_bounds__(PB_THREADS) preprocess_backward_kernel(PreprocessBackwardParams p)
+{
+    __shared__ float s_view[16], s_proj[16], s_cam[3];
+    if (threadIdx.x < 16) {
+        s_view[threadIdx.x] = p.viewmatrix[threadIdx.x];
+        s_proj[threadIdx.x] = p.projmatrix[threadIdx.x];
+    }
+    if (threadIdx.x < 3) s_cam[threadIdx.x] = p.cam_pos[threadIdx.x];
+    __syncthreads();
+
+    const int idx = blockIdx.x * PB_THREADS + threadIdx.x;
+    if (idx >= p.P) return;
+    const size_t i = (size_t)idx;
+    const int ncoef = (p.D + 1) * (p.D + 1);
+
+    if (!(p.radii[idx] > 0)) {
+        store3(p.dL_dmean2D + 3 * i, 0.f, 0.f, 0.f);
+        store3(p.dL_dcolor + 3 * i, 0.f, 0.f, 0.f);
+        p.dL_dopacity[i] = 0.f;
+        store3(p.dL_dmean3D + 3 * i, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int k = 0; k < 6; ++k) p.dL_dcov3D[6 * i + k] = 0.f;
+        store3(p.dL_dscale + 3 * i, 0.f, 0.f, 0.f);
+        if ((reinterpret_cast<uintptr_t>(p.dL_drot) & 15) == 0) {
+            reinterpret_cast<float4*>(p.dL_drot)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) p.dL_drot[4 * i + k] = 0.f;
+        }
+        if (p.M > 0) {
+            if (kVecSH) {
+                float4* dst = reinterpret_cast<float4*>(p.dL_dsh) + i * 12;
+#pragma unroll
+                for (int k = 0; k < 12; ++k) dst[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+            } else {
+                float* dst = p.dL_dsh + i * p.M * 3;
+                for (int k = 0; k < p.M * 3; ++k) dst[k] = 0.f;
+            }
+        }
+        return;
+    }
+
+    // ---- screen-space gradients accumulated by the backward render ---------------------------
+    const float4* arow = reinterpret_cast<const float4*>(p.acc + i * ACC_STRIDE);
+    const float4 a0 = arow[0], a1 = arow[1], a2 = arow[2];
+    const float gmx = a0.x, gmy = a0.y;               // dL/dmean2D
+    const float gcx = a0.z, gcy = a0.w, gcw = a1.x;   // dL/dconic (x, y, w)
+    const float gop = a1.y;
+    const V3 gcol = v3(a1.z, a1.w, a2.x);
+    store3(p.dL_dmean2D + 3 * i, gmx, gmy, 0.f);
+    store3(p.dL_dcolor + 3 * i, gcol.x, gcol.y, gcol.z);
+    p.dL_dopacity[i] = gop;
+
+    const float3 mean = {p.means3D[3 * i], p.means3D[3 * i + 1], p.means3D[3 * i + 2]};
+
+    // ---- 3D covariance exactly as the forward saw it ------------------------------------------
+    float cov3D[6];
+    float3 sc = {0.f, 0.f, 0.f};
+    float4 q = {0.f, 0.f, 0.f, 0.f};
+    if (p.scales != nullptr) {
+        sc = float3{p.scales[3 * i], p.scales[3 * i + 1], p.scales[3 * i + 2]};
+        q = float4{p.rotations[4 * i], p.rotations[4 * i + 1], p.rotations[4 * i + 2],
+                   p.rotations[4 * i + 3]};
+    }
+    if (p.cov3D_precomp != nullptr) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) cov3D[k] = p.cov3D_precomp[6 * i + k];
+    } else {
+        cov3d_from_scale_rot(sc, p.scale_modifier, q, cov3D);
+    }
+
+    // ---- K6: conic -> cov2D -> (cov3D, T) -> J -> view-space mean -----------------------------
+    const ProjFrame f = make_proj_frame(mean, p.focal_x, p.focal_y, p.tan_fovx, p.tan_fovy, s_view);
+    const float limx = 1.3f * p.tan_fovx, limy = 1.3f * p.tan_fovy;
+    const float x_grad_mul = (f.txtz < -limx || f.txtz > limx) ? 0.f : 1.f;
+    const float y_grad_mul = (f.tytz < -limy || f.tytz > limy) ? 0.f : 1.f;
+    const M3 cov2D = cov2d_full(f.T, cov3D);
+    const float a = cov2D.m[0][0] + 0.3f;
+    const float b = cov2D.m[0][1];
+    const float c = cov2D.m[1][1] + 0.3f;
+
+    // t0 / t1: the two 3-vectors with cov2D = [t0.V.t0, t0.V.t1; ., t1.V.t1]
+    const V3 t0 = v3(f.T.m[0][0], f.T.m[0][1], f.T.m[0][2]);
+    const V3 t1 = v3(f.T.m[1][0], f.T.m[1][1], f.T.m[1][2]);
+
+    const float denom = a * c - b * b;
+    const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+    float dL_da = 0.f, dL_db = 0.f, dL_dc = 0.f;
+    float dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (denom2inv != 0) {
+        dL_da = denom2inv * (-c * c * gcx + 2 * b * c * gcy + (denom - a * c) * gcw);
+        dL_dc = denom2inv * (-a * a * gcw + 2 * a * b * gcy + (denom - a * c) * gcx);
+        dL_db = denom2inv * 2 * (b * c * gcx - (denom + 2 * b * b) * gcy + a * b * gcw);
+        // diagonal entries of the symmetric 3D covariance, then the doubled off-diagonals
+        dcov[0] = t0.x * t0.x * dL_da + t0.x * t1.x * dL_db + t1.x * t1.x * dL_dc;
+        dcov[3] = t0.y * t0.y * dL_da + t0.y * t1.y * dL_db + t1.y * t1.y * dL_dc;
+        dcov[5] = t0.z * t0.z * dL_da + t0.z * t1.z * dL_db + t1.z * t1.z * dL_dc;
+        dcov[1] = 2 * t0.x * t0.y * dL_da + (t0.x * t1.y + t0.y * t1.x) * dL_db + 2 * t1.x * t1.y * dL_dc;
+        dcov[2] = 2 * t0.x * t0.z * dL_da + (t0.x * t1.z + t0.z * t1.x) * dL_db + 2 * t1.x * t1.z * dL_dc;
+        dcov[4] = 2 * t0.z * t0.y * dL_da + (t0.y * t1.z + t0.z * t1.y) * dL_db + 2 * t1.y * t1.z * dL_dc;
+    }
+#pragma unroll
+    for (int k = 0; k < 6; ++k) p.dL_dcov3D[6 * i + k] = dcov[k];
+
+    // V.t0 and V.t1 (V symmetric)
+    const V3 Vt0 = v3(cov3D[0] * t0.x + cov3D[1] * t0.y + cov3D[2] * t0.z,
+                      cov3D[1] * t0.x + cov3D[3] * t0.y + cov3D[4] * t0.z,
+                      cov3D[2] * t0.x + cov3D[4] * t0.y + cov3D[5] * t0.z);
+    const V3 Vt1 = v3(cov3D[0] * t1.x + cov3D[1] * t1.y + cov3D[2] * t1.z,
+                      cov3D[1] * t1.x + cov3D[3] * t1.y + cov3D[4] * t1.z,
+                      cov3D[2] * t1.x + cov3D[4] * t1.y + cov3D[5] * t1.z);
+    const V3 dT0 = (2 * dL_da) * Vt0 + dL_db * Vt1;
+    const V3 dT1 = (2 * dL_dc) * Vt1 + dL_db * Vt0;
+
+    // T = W * J  =>  dL/dJ[c][k] = sum_r W[k][r] * dL/dT[c][r]
+    const M3& Wm = f.W;
+    const float dL_dJ00 = Wm.m[0][0] * dT0.x + Wm.m[0][1] * dT0.y + Wm.m[0][2] * dT0.z;
+    const float dL_dJ02 = Wm.m[2][0] * dT0.x + Wm.m[2][1] * dT0.y + Wm.m[2][2] * dT0.z;
+    const float dL_dJ11 = Wm.m[1][0] * dT1.x + Wm.m[1][1] * dT1.y + Wm.m[1][2] * dT1.z;
+    const float dL_dJ12 = Wm.m[2][0] * dT1.x + Wm.m[2][1] * dT1.y + Wm.m[2][2] * dT1.z;
+
+    const float tz = 1.f / f.t.z;
+    const float tz2 = tz * tz;
+    const float tz3 = tz2 * tz;
+    const float dL_dtx = x_grad_mul * -p.focal_x * tz2 * dL_dJ02;
+    const float dL_dty = y_grad_mul * -p.focal_y * tz2 * dL_dJ12;
+    const float dL_dtz = -p.focal_x * tz2 * dL_dJ00 - p.focal_y * tz2 * dL_dJ11 +
+                         (2 * p.focal_x * f.t.x) * tz3 * dL_dJ02 +
+                         (2 * p.focal_y * f.t.y) * tz3 * dL_dJ12;
+    // back through t = view * mean (rotation part transposed)
+    V3 dmean = v3(s_view[0] * dL_dtx + s_view[1] * dL_dty + s_view[2] * dL_dtz,
+                  s_view[4] * dL_dtx + s_view[5] * dL_dty + s_view[6] * dL_dtz,
+                  s_view[8] * dL_dtx + s_view[9] * dL_dty + s_view[10] * dL_dtz);
+
+    // ---- K7a: screen-space mean -> 3D mean through the perspective divide ---------------------
+    {
+        const float4 m_hom = xform_4x4(mean, s_proj);
+        const float m_w = 1.0f / (m_hom.w + 0.0000001f);
+        const float mul1 = (s_proj[0] * mean.x + s_proj[4] * mean.y + s_proj[8] * mean.z + s_proj[12]) * m_w * m_w;
+        const float mul2 = (s_proj[1] * mean.x + s_proj[5] * mean.y + s_proj[9] * mean.z + s_proj[13]) * m_w * m_w;
+        V3 d;
+        d.x = (s_proj[0] * m_w - s_proj[3] * mul1) * gmx + (s_proj[1] * m_w - s_proj[3] * mul2) * gmy;
+        d.y = (s_proj[4] * m_w - s_proj[7] * mul1) * gmx + (s_proj[5] * m_w - s_proj[7] * mul2) * gmy;
+        d.z = (s_proj[8] * m_w - s_proj[11] * mul1) * gmx + (s_proj[9] * m_w - s_proj[11] * mul2) * gmy;
+        dmean = dmean + d;
+    }
+
+    // ---- K7b: colour -> SH coefficients and view direction ------------------------------------
+    if (p.shs != nullptr) {
+        const uint32_t clampbits = __float_as_uint(__ldg(&p.rec[idx].q2).w);
+        V3 dRGB = gcol;
+        if (clampbits & 1u) dRGB.x = 0.f;
+        if (clampbits & 2u) dRGB.y = 0.f;
+        if (clampbits & 4u) dRGB.z = 0.f;
+
+        const V3 dir_orig = v3(mean.x, mean.y, mean.z) - v3(s_cam[0], s_cam[1], s_cam[2]);
+        const V3 dir = dir_orig / length3(dir_orig);
+        const float x = dir.x, y = dir.y, z = dir.z;
+        const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+
+        // basis values and their partial derivatives w.r.t. the unit direction
+        float bas[16], bx[16], by[16], bz[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) { bas[k] = 0.f; bx[k] = 0.f; by[k] = 0.f; bz[k] = 0.f; }
+        bas[0] = kC0;
+        bas[1] = -kC1 * y;                 by[1] = -kC1;
+        bas[2] = kC1 * z;                  bz[2] = kC1;
+        bas[3] = -kC1 * x;                 bx[3] = -kC1;
+        bas[4] = kC2_0 * xy;               bx[4] = kC2_0 * y;          by[4] = kC2_0 * x;
+        bas[5] = kC2_1 * yz;               by[5] = kC2_1 * z;          bz[5] = kC2_1 * y;
+        bas[6] = kC2_2 * (2.f * zz - xx - yy);
+        bx[6] = kC2_2 * 2.f * -x;          by[6] = kC2_2 * 2.f * -y;   bz[6] = kC2_2 * 2.f * 2.f * z;
+        bas[7] = kC2_3 * xz;               bx[7] = kC2_3 * z;          bz[7] = kC2_3 * x;
+        bas[8] = kC2_4 * (xx - yy);        bx[8] = kC2_4 * 2.f * x;    by[8] = kC2_4 * 2.f * -y;
+        bas[9] = kC3_0 * y * (3.f * xx - yy);
+        bx[9] = kC3_0 * 3.f * 2.f * xy;    by[9] = kC3_0 * 3.f * (xx - yy);
+        bas[10] = kC3_1 * xy * z;
+        bx[10] = kC3_1 * yz;               by[10] = kC3_1 * xz;        bz[10] = kC3_1 * xy;
+        bas[11] = kC3_2 * y * (4.f * zz - xx - yy);
+        bx[11] = kC3_2 * -2.f * xy;        by[11] = kC3_2 * (-3.f * yy + 4.f * zz - xx);
+        bz[11] = kC3_2 * 4.f * 2.f * yz;
+        bas[12] = kC3_3 * z * (2.f * zz - 3.f * xx - 3.f * yy);
+        bx[12] = kC3_3 * -3.f * 2.f * xz;  by[12] = kC3_3 * -3.f * 2.f * yz;
+        bz[12] = kC3_3 * 3.f * (2.f * zz - xx - yy);
+        bas[13] = kC3_4 * x * (4.f * zz - xx - yy);
+        bx[13] = kC3_4 * (-3.f * xx + 4.f * zz - yy);  by[13] = kC3_4 * -2.f * xy;
+        bz[13] = kC3_4 * 4.f * 2.f * xz;
+        bas[14] = kC3_5 * z * (xx - yy);
+        bx[14] = kC3_5 * 2.f * xz;         by[14] = kC3_5 * -2.f * yz; bz[14] = kC3_5 * (xx - yy);
+        bas[15] = kC3_6 * x * (xx - 3.f * yy);
+        bx[15] = kC3_6 * 3.f * (xx - yy);  by[15] = kC3_6 * -3.f * 2.f * xy;
+
+        V3 dRGBdx = v3(0.f, 0.f, 0.f), dRGBdy = v3(0.f, 0.f, 0.f), dRGBdz = v3(0.f, 0.f, 0.f);
+        if (kVecSH) {
+            // 48 floats in, 48 floats out, as 12 + 12 128-bit accesses
+            const float4* src = reinterpret_cast<const float4*>(p.shs) + i * 12;
+            float4* dst = reinterpret_cast<float4*>(p.dL_dsh) + i * 12;
+            float sh[48], out[48];
+            const int nvec = (3 * ncoef + 3) >> 2;
+#pragma unroll
+            for (int k = 0; k < 12; ++k) {
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (k < nvec) v = __ldg(src + k);
+                sh[4 * k] = v.x; sh[4 * k + 1] = v.y; sh[4 * k + 2] = v.z; sh[4 * k + 3] = v.w;
+            }
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                const bool on = k < ncoef;
+                const float bk = on ? bas[k] : 0.f;
+                out[3 * k] = bk * dRGB.x; out[3 * k + 1] = bk * dRGB.y; out[3 * k + 2] = bk * dRGB.z;
+                if (on && k > 0) {
+                    const V3 s = v3(sh[3 * k], sh[3 * k + 1], sh[3 * k + 2]);
+                    dRGBdx = dRGBdx + bx[k] * s;
+                    dRGBdy = dRGBdy + by[k] * s;
+                    dRGBdz = dRGBdz + bz[k] * s;
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < 12; ++k)
+                dst[k] = make_float4(out[4 * k], out[4 * k + 1], out[4 * k + 2], out[4 * k + 3]);
+        } else {
+            const float* src = p.shs + i * p.M * 3;
+            float* dst = p.dL_dsh + i * p.M * 3;
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                if (k < p.M) {
+                    const bool on = k < ncoef;
+                    const float bk = on ? bas[k] : 0.f;
+                    dst[3 * k] = bk * dRGB.x; dst[3 * k + 1] = bk * dRGB.y; dst[3 * k + 2] = bk * dRGB.z;
+                    if (on && k > 0) {
+                        const V3 s = v3(src[3 * k], src[3 * k + 1], src[3 * k + 2]);
+                        dRGBdx = dRGBdx + bx[k] * s;
+                        dRGBdy = dRGBdy + by[k] * s;
+                        dRGBdz = dRGBdz + bz[k] * s;
+                    }
+                }
+            }
+            for (int k = 16; k < p.M; ++k) store3(dst + 3 * k, 0.f, 0.f, 0.f);
+        }
+
+        const V3 dL_ddir = v3(dot3(dRGBdx, dRGB), dot3(dRGBdy, dRGB), dot3(dRGBdz, dRGB));
+        // derivative of v/|v|
+        const V3 v = dir_orig;
+        const float sum2 = v.x * v.x + v.y * v.y + v.z * v.z;
+        const float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
+        V3 dn;
+        dn.x = ((+sum2 - v.x * v.x) * dL_ddir.x - v.y * v.x * dL_ddir.y - v.z * v.x * dL_ddir.z) * invsum32;
+        dn.y = (-v.x * v.y * dL_ddir.x + (sum2 - v.y * v.y) * dL_ddir.y - v.z * v.y * dL_ddir.z) * invsum32;
+        dn.z = (-v.x * v.z * dL_ddir.x - v.y * v.z * dL_ddir.y + (sum2 - v.z * v.z) * dL_ddir.z) * invsum32;
+        dmean = dmean + dn;
+    }
+    store3(p.dL_dmean3D + 3 * i, dmean.x, dmean.y, dmean.z);
+
+    // ---- K7c: 3D covariance -> scale and (unnormalised) quaternion ----------------------------
+    if (p.scales != nullptr) {
+        const float r = q.x, x = q.y, y = q.z, z = q.w;
+        const M3 Rg = quat_to_m3(r, x, y, z);
+        // Rs[a][b]: row a, column b of the matrix the reference calls R (Rg is column-major)
+        float Rs[3][3], Ms[3][3];
+        const float s[3] = {p.scale_modifier * sc.x, p.scale_modifier * sc.y, p.scale_modifier * sc.z};
+#pragma unroll
+        for (int aa = 0; aa < 3; ++aa)
+#pragma unroll
+            for (int bb = 0; bb < 3; ++bb) {
+                Rs[aa][bb] = Rg.m[bb][aa];
+                Ms[aa][bb] = s[aa] * Rs[aa][bb];
+            }
+        // symmetric dL/dSigma with halved off-diagonals
+        const float dS[3][3] = {{dcov[0], 0.5f * dcov[1], 0.5f * dcov[2]},
+                                {0.5f * dcov[1], dcov[3], 0.5f * dcov[4]},
+                                {0.5f * dcov[2], 0.5f * dcov[4], dcov[5]}};
+        float dM[3][3];  // dL/dM = 2 M dSigma
+#pragma unroll
+        for (int aa = 0; aa < 3; ++aa)
+#pragma unroll
+            for (int bb = 0; bb < 3; ++bb)
+                dM[aa][bb] = 2.0f * Ms[aa][0] * dS[0][bb] + 2.0f * Ms[aa][1] * dS[1][bb] +
+                             2.0f * Ms[aa][2] * dS[2][bb];
+        float dscale[3];
+        float Gm[3][3];  // dL/dR
+#pragma unroll
+        for (int aa = 0; aa < 3; ++aa) {
+            dscale[aa] = Rs[aa][0] * dM[aa][0] + Rs[aa][1] * dM[aa][1] + Rs[aa][2] * dM[aa][2];
+#pragma unroll
+            for (int bb = 0; bb < 3; ++bb) Gm[aa][bb] = s[aa] * dM[aa][bb];
+        }
+        store3(p.dL_dscale + 3 * i, dscale[0], dscale[1], dscale[2]);
+
+        float4 dq;
+        dq.x = 2 * z * (Gm[0][1] - Gm[1][0]) + 2 * y * (Gm[2][0] - Gm[0][2]) + 2 * x * (Gm[1][2] - Gm[2][1]);
+        dq.y = 2 * y * (Gm[1][0] + Gm[0][1]) + 2 * z * (Gm[2][0] + Gm[0][2]) + 2 * r * (Gm[1][2] - Gm[2][1]) - 4 * x * (Gm[2][2] + Gm[1][1]);
+        dq.z = 2 * x * (Gm[1][0] + Gm[0][1]) + 2 * r * (Gm[2][0] - Gm[0][2]) + 2 * z * (Gm[1][2] + Gm[2][1]) - 4 * y * (Gm[2][2] + Gm[0][0]);
+        dq.w = 2 * r * (Gm[0][1] - Gm[1][0]) + 2 * x * (Gm[2][0] + Gm[0][2]) + 2 * y * (Gm[1][2] + Gm[2][1]) - 4 * z * (Gm[1][1] + Gm[0][0]);
+        if ((reinterpret_cast<uintptr_t>(p.dL_drot) & 15) == 0) {
+            reinterpret_cast<float4*>(p.dL_drot)[i] = dq;
+        } else {
+            p.dL_drot[4 * i] = dq.x; p.dL_drot[4 * i + 1] = dq.y;
+            p.dL_drot[4 * i + 2] = dq.z; p.dL_drot[4 * i + 3] = dq.w;
+        }
+    } else {
+        store3(p.dL_dscale + 3 * i, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) p.dL_drot[4 * i + k] = 0.f;
+    }
+}
+
+}  // namespace
+
+void launch_preprocess_backward(const PreprocessBackwardParams& p, cudaStream_t s)
+{
+    if (p.P <= 0) return;
+    const int blocks = (p.P + PB_THREADS - 1) / PB_THREADS;
+    const bool vec = p.shs != nullptr && p.M == 16 &&
+                     (reinterpret_cast<uintptr_t>(p.shs) & 15) == 0 &&
+                     (reinterpret_cast<uintptr_t>(p.dL_dsh) & 15) == 0;
+    if (vec)
+        preprocess_backward_kernel<true><<<blocks, PB_THREADS, 0, s>>>(p);
+    else
+        preprocess_backward_kernel<false><<<blocks, PB_THREADS, 0, s>>>(p);
+}
+
+}  // namespace bgr

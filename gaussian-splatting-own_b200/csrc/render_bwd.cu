@@ -1,0 +1,211 @@
+// Backward tile renderer (K5): back-to-front re-traversal producing per-Gaussian screen-space
+// gradients (dL/dmean2D, dL/dconic, dL/dopacity, dL/dcolour).
+//
+// Spec: SURVEY.md App. A.8 (reference backward.cu:399-557). The set of (pixel, splat) pairs that
+// contribute is decided by the same bit-exact tests as the forward pass; gradient values are
+// tolerance-level (the reference accumulates them with unordered float atomics).
+//
+// Differences from the reference:
+//  * only list entries below the tile's maximum n_contrib are visited at all;
+//  * same record gather + conservative tile rejection + ordered compaction as the forward;
+//  * the inner loop is warp-uniform: a splat that no lane of the warp blends is skipped by one
+//    vote; otherwise the nine per-pixel gradient terms are reduced across the warp with a
+//    transposing butterfly (14 shuffles instead of 45) and leave the SM as ONE reduction per
+//    component per (warp, splat) instead of one per (pixel, splat): 9 REDs instead of up to 288;
+//  * the accumulators live in one 48-byte AoS row per Gaussian (bgr_common.cuh ACC_STRIDE) that the
+//    fused backward preprocess consumes directly.
+#include "render_common.cuh"
+
+namespace bgr {
+
+namespace {
+
+__global__ void __launch_bounds__(RENDER_THREADS)
+render_backward_kernel(int W, int H, const uint2* __restrict__ ranges,
+                       const uint32_t* __restrict__ point_list, const GaussRec* __restrict__ rec,
+                       const float* __restrict__ bg, const float* __restrict__ final_T,
+                       const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix,
+                       float* __restrict__ acc)
+{
+    __shared__ float4 s_q0[RENDER_THREADS];   // x, y, conic.x, conic.y
+    __shared__ float4 s_q1[RENDER_THREADS];   // conic.z, opacity, r, g
+    __shared__ float4 s_q2[RENDER_THREADS];   // b, thr, list position (bits), Gaussian id (bits)
+    __shared__ uint32_t s_warp_count[RENDER_WARPS];
+    __shared__ uint32_t s_warp_max[RENDER_WARPS];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t tiles_x = (W + TILE_X - 1) / TILE_X;
+    const uint32_t tile_px = blockIdx.x * TILE_X, tile_py = blockIdx.y * TILE_Y;
+    int lx, ly;
+    tile_pixel(tid, lx, ly);
+    const uint32_t px = tile_px + lx, py = tile_py + ly;
+    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
+    const size_t pix_id = (size_t)py * W + px;
+    const float pixfx = (float)px, pixfy = (float)py;
+    const float rx0 = (float)tile_px, ry0 = (float)tile_py;
+    const float rx1 = (float)min(tile_px + TILE_X - 1, (uint32_t)W - 1);
+    const float ry1 = (float)min(tile_py + TILE_Y - 1, (uint32_t)H - 1);
+
+    const uint2 range = ranges[blockIdx.y * tiles_x + blockIdx.x];
+
+    const float T_final = inside ? final_T[pix_id] : 0.0f;
+    float T = T_final;
+    const uint32_t last_contributor = inside ? n_contrib[pix_id] : 0u;
+
+    // Entries at or beyond the largest n_contrib of the tile cannot contribute to any pixel.
+    const uint32_t wmax = __reduce_max_sync(0xffffffffu, last_contributor);
+    if (lane == 0) s_warp_max[warp] = wmax;
+    __syncthreads();
+    uint32_t total_u = 0;
+#pragma unroll
+    for (int w = 0; w < RENDER_WARPS; ++w) total_u = max(total_u, s_warp_max[w]);
+    total_u = min(total_u, range.y - range.x);
+    const int total = (int)total_u;
+    if (total == 0) return;
+    const int rounds = (total + RENDER_THREADS - 1) / RENDER_THREADS;
+
+    float accum0 = 0.f, accum1 = 0.f, accum2 = 0.f;
+    float last_alpha = 0.f;
+    float lastc0 = 0.f, lastc1 = 0.f, lastc2 = 0.f;
+    float g0 = 0.f, g1 = 0.f, g2 = 0.f;
+    if (inside) {
+        const size_t plane = (size_t)H * W;
+        g0 = dL_dpix[pix_id];
+        g1 = dL_dpix[plane + pix_id];
+        g2 = dL_dpix[2 * plane + pix_id];
+    }
+    const float bg_dot_dpixel = bg[0] * g0 + bg[1] * g1 + bg[2] * g2;
+    const float ddelx_dx = 0.5f * W;
+    const float ddely_dy = 0.5f * H;
+
+    for (int r = 0; r < rounds; ++r) {
+        __syncthreads();
+        const int progress = r * RENDER_THREADS + tid;
+        bool keep = false;
+        float4 q0, q1, q2;
+        uint32_t id = 0, li = 0;
+        if (progress < total) {
+            li = (uint32_t)(total - 1 - progress);  // back to front
+            id = point_list[range.x + li];
+            const GaussRec* g = rec + id;
+            q0 = __ldg(&g->q0);
+            q1 = __ldg(&g->q1);
+            q2 = __ldg(&g->q2);
+            keep = !tile_rejects(q0.x, q0.y, q0.z, q0.w, q1.x, q2.y, rx0, ry0, rx1, ry1);
+        }
+        const unsigned kmask = __ballot_sync(0xffffffffu, keep);
+        if (lane == 0) s_warp_count[warp] = __popc(kmask);
+        __syncthreads();
+        int before = 0, kept = 0;
+#pragma unroll
+        for (int w = 0; w < RENDER_WARPS; ++w) {
+            const int c = (int)s_warp_count[w];
+            if (w < warp) before += c;
+            kept += c;
+        }
+        if (keep) {
+            const int pos = before + __popc(kmask & ((1u << lane) - 1u));
+            s_q0[pos] = q0;
+            s_q1[pos] = q1;
+            s_q2[pos] = make_float4(q2.x, q2.y, __uint_as_float(li), __uint_as_float(id));
+        }
+        __syncthreads();
+
+        for (int j = 0; j < kept; ++j) {
+            const float4 a = s_q0[j];
+            const float4 b = s_q1[j];
+            const float4 c = s_q2[j];
+            const uint32_t pos_in_list = __float_as_uint(c.z);
+            bool valid = pos_in_list < last_contributor;  // false for pixels outside the image
+            const float dx = a.x - pixfx;
+            const float dy = a.y - pixfy;
+            const float power = gauss_power(a.z, a.w, b.x, dx, dy);
+            valid = valid && !(power > 0.0f || power < c.y);
+            if (!__any_sync(0xffffffffu, valid)) continue;
+            const float G = expf(power);
+            const float alpha = fminf(0.99f, b.y * G);
+            valid = valid && !(alpha < 1.0f / 255.0f);
+            if (!__any_sync(0xffffffffu, valid)) continue;
+
+            float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f, v4 = 0.f, v5 = 0.f, v6 = 0.f, v7 = 0.f,
+                  v8 = 0.f;
+            if (valid) {
+                const float one_m_alpha = 1.f - alpha;
+                T = T / one_m_alpha;
+                const float dchannel_dcolor = alpha * T;
+                float dL_dalpha = 0.0f;
+                const float one_m_last = 1.f - last_alpha;
+                accum0 = last_alpha * lastc0 + one_m_last * accum0;
+                lastc0 = b.z;
+                dL_dalpha += (b.z - accum0) * g0;
+                accum1 = last_alpha * lastc1 + one_m_last * accum1;
+                lastc1 = b.w;
+                dL_dalpha += (b.w - accum1) * g1;
+                accum2 = last_alpha * lastc2 + one_m_last * accum2;
+                lastc2 = c.x;
+                dL_dalpha += (c.x - accum2) * g2;
+                dL_dalpha *= T;
+                last_alpha = alpha;
+                dL_dalpha += (-T_final / one_m_alpha) * bg_dot_dpixel;
+
+                const float dL_dG = b.y * dL_dalpha;
+                const float gdx = G * dx;
+                const float gdy = G * dy;
+                const float dG_ddelx = -gdx * a.z - gdy * a.w;
+                const float dG_ddely = -gdy * b.x - gdx * a.w;
+                v0 = dL_dG * dG_ddelx * ddelx_dx;
+                v1 = dL_dG * dG_ddely * ddely_dy;
+                v2 = -0.5f * gdx * dx * dL_dG;
+                v3 = -0.5f * gdx * dy * dL_dG;
+                v4 = -0.5f * gdy * dy * dL_dG;
+                v5 = G * dL_dalpha;
+                v6 = dchannel_dcolor * g0;
+                v7 = dchannel_dcolor * g1;
+                v8 = dchannel_dcolor * g2;
+            }
+
+            // Transposing butterfly: 8 values x 32 lanes -> each value summed over the warp.
+            const bool h1 = (lane & 16) != 0;
+            float w0 = (h1 ? v4 : v0) + __shfl_xor_sync(0xffffffffu, h1 ? v0 : v4, 16);
+            float w1 = (h1 ? v5 : v1) + __shfl_xor_sync(0xffffffffu, h1 ? v1 : v5, 16);
+            float w2 = (h1 ? v6 : v2) + __shfl_xor_sync(0xffffffffu, h1 ? v2 : v6, 16);
+            float w3 = (h1 ? v7 : v3) + __shfl_xor_sync(0xffffffffu, h1 ? v3 : v7, 16);
+            const bool h2 = (lane & 8) != 0;
+            float u0 = (h2 ? w2 : w0) + __shfl_xor_sync(0xffffffffu, h2 ? w0 : w2, 8);
+            float u1 = (h2 ? w3 : w1) + __shfl_xor_sync(0xffffffffu, h2 ? w1 : w3, 8);
+            const bool h3 = (lane & 4) != 0;
+            float sacc = (h3 ? u1 : u0) + __shfl_xor_sync(0xffffffffu, h3 ? u0 : u1, 4);
+            sacc += __shfl_xor_sync(0xffffffffu, sacc, 2);
+            sacc += __shfl_xor_sync(0xffffffffu, sacc, 1);
+            // ninth value: plain butterfly
+            v8 += __shfl_xor_sync(0xffffffffu, v8, 16);
+            v8 += __shfl_xor_sync(0xffffffffu, v8, 8);
+            v8 += __shfl_xor_sync(0xffffffffu, v8, 4);
+            v8 += __shfl_xor_sync(0xffffffffu, v8, 2);
+            v8 += __shfl_xor_sync(0xffffffffu, v8, 1);
+
+            float* row = acc + (size_t)__float_as_uint(c.w) * ACC_STRIDE;
+            // lane 4k holds value index k = bit2 + 2*bit3 + 4*bit4 of the lane id
+            if ((lane & 3) == 0) {
+                const int vi = ((lane >> 2) & 1) | (((lane >> 3) & 1) << 1) | (((lane >> 4) & 1) << 2);
+                atomicAdd(row + vi, sacc);
+            } else if (lane == 1) {
+                atomicAdd(row + 8, v8);
+            }
+        }
+    }
+}
+
+}  // namespace
+
+void launch_render_backward(int W, int H, const uint2* ranges, const uint32_t* point_list,
+                            const GaussRec* rec, const float* /*colors_precomp*/, const float* bg,
+                            const float* final_T, const uint32_t* n_contrib, const float* dL_dpix,
+                            float* acc, cudaStream_t s)
+{
+    const dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1);
+    render_backward_kernel<<<grid, RENDER_THREADS, 0, s>>>(W, H, ranges, point_list, rec, bg, final_T,
+                                                          n_contrib, dL_dpix, acc);
+}
+
+}  // namespace bgr

@@ -1,0 +1,76 @@
+// Shared pieces of the forward and backward tile renderers.
+#pragma once
+#include "bgr_common.cuh"
+
+namespace bgr {
+
+constexpr int RENDER_THREADS = TILE_PIXELS;  // one thread per pixel of the 16x16 tile
+constexpr int RENDER_WARPS = RENDER_THREADS / 32;
+
+// Thread -> pixel mapping inside the tile: each warp owns an 8x4 pixel block (instead of a 16x2
+// strip) so that the per-warp skip of non-overlapping splats is tighter. The mapping does not
+// change any result; every pixel is still computed by exactly one thread.
+__device__ __forceinline__ void tile_pixel(int tid, int& lx, int& ly)
+{
+    const int warp = tid >> 5, lane = tid & 31;
+    lx = ((warp & 1) << 3) | (lane & 7);
+    ly = ((warp >> 1) << 2) | (lane >> 3);
+}
+
+// Exactly the reference's evaluation order for the Gaussian exponent (forward.cu:335, SASS shape in
+// SURVEY.md A.5): power = -0.5*(cx*dx*dx + cz*dy*dy) - cy*dx*dy with
+//   t = (cz*dy)*dy, u = cx*dx, q = fma(u,dx,t), v = (cy*dx)*dy, power = fma(-0.5,q,-v).
+__device__ __forceinline__ float gauss_power(float cx, float cy, float cz, float dx, float dy)
+{
+    const float t = __fmul_rn(__fmul_rn(cz, dy), dy);
+    const float u = __fmul_rn(cx, dx);
+    const float q = __fmaf_rn(u, dx, t);
+    const float v = __fmul_rn(__fmul_rn(cy, dx), dy);
+    return __fmaf_rn(-0.5f, q, -v);
+}
+
+// Conservative tile-level rejection. Returns true when NO pixel centre of the rectangle
+// [px0,px1]x[py0,py1] can pass the reference's per-pixel tests (power <= 0 and
+// opacity*exp(power) >= 1/255), so dropping the splat from this tile's working list cannot change
+// any pixel. q(d) = -power is a convex quadratic when the conic is positive definite; its minimum
+// over the rectangle is 0 if the centre is inside, otherwise it lies on one of the (at most two)
+// edges facing the centre, where it is a 1-D quadratic with a clamped closed-form minimiser.
+// Everything non-finite or not positive definite is kept (all comparisons are written so that NaN
+// evaluates to "keep"). The tolerance covers the rounding difference between this bound and the
+// exact per-pixel evaluation.
+__device__ __forceinline__ bool tile_rejects(float mx, float my, float cx, float cy, float cz,
+                                             float thr, float px0, float py0, float px1, float py1)
+{
+    // d = mean - pixel: intervals of dx, dy over the rectangle
+    const float dx_lo = mx - px1, dx_hi = mx - px0;
+    const float dy_lo = my - py1, dy_hi = my - py0;
+    const bool in_x = (dx_lo <= 0.0f) && (dx_hi >= 0.0f);
+    const bool in_y = (dy_lo <= 0.0f) && (dy_hi >= 0.0f);
+    const float det = cx * cz - cy * cy;
+    if (!(cx > 0.0f) || !(cz > 0.0f) || !(det > 0.0f)) return false;
+    if (in_x && in_y) return false;
+    const float tau = -thr;  // ln(255*opacity) + margin
+    if (!(tau == tau)) return false;
+    float qmin = 3.0e38f;
+    float mag = 0.0f;
+    if (!in_x) {
+        // vertical edge facing the centre: dx = e fixed, minimise over dy
+        const float e = (dx_lo > 0.0f) ? dx_lo : dx_hi;
+        float dy = -cy * e / cz;
+        dy = fminf(fmaxf(dy, dy_lo), dy_hi);
+        const float a = 0.5f * cx * e * e, b = 0.5f * cz * dy * dy, c = cy * e * dy;
+        const float q = a + b + c;
+        if (q < qmin) { qmin = q; mag = fabsf(a) + fabsf(b) + fabsf(c); }
+    }
+    if (!in_y) {
+        const float e = (dy_lo > 0.0f) ? dy_lo : dy_hi;
+        float dx = -cy * e / cx;
+        dx = fminf(fmaxf(dx, dx_lo), dx_hi);
+        const float a = 0.5f * cz * e * e, b = 0.5f * cx * dx * dx, c = cy * e * dx;
+        const float q = a + b + c;
+        if (q < qmin) { qmin = q; mag = fabsf(a) + fabsf(b) + fabsf(c); }
+    }
+    return qmin > tau + 1e-3f + 8e-6f * mag;
+}
+
+}  // namespace bgr

@@ -1,0 +1,134 @@
+// Forward tile renderer (K4): front-to-back alpha compositing of the depth-sorted per-tile lists.
+//
+// Spec: SURVEY.md App. A.4 (reference forward.cu:261-374). Per-pixel arithmetic (power, expf,
+// alpha clamp, 1/255 skip, T < 1e-4 stop, colour FMA order) follows the reference instruction for
+// instruction so that n_contrib is bit-identical and the image matches to rounding.
+//
+// What is different from the reference:
+//  * the cooperative fetch gathers ONE 48-byte record per list entry (position, conic, opacity,
+//    colour) instead of three arrays + three dependent global colour loads inside the pixel loop;
+//  * the fetching thread runs an exact-conservative splat/tile rejection test (render_common.cuh)
+//    and the batch is order-preservingly compacted in shared memory (ballot + prefix), so the
+//    256 pixel threads only iterate over splats that can reach alpha >= 1/255 somewhere in the tile;
+//  * per pair, a single compare against the precomputed log-threshold skips the expf for pairs
+//    whose alpha is provably < 1/255;
+//  * warps own 8x4 pixel blocks.
+#include "render_common.cuh"
+
+namespace bgr {
+
+namespace {
+
+__global__ void __launch_bounds__(RENDER_THREADS)
+render_forward_kernel(int W, int H, const uint2* __restrict__ ranges,
+                      const uint32_t* __restrict__ point_list, const GaussRec* __restrict__ rec,
+                      const float* __restrict__ bg, float* __restrict__ final_T,
+                      uint32_t* __restrict__ n_contrib, float* __restrict__ out_color)
+{
+    __shared__ float4 s_q0[RENDER_THREADS];   // x, y, conic.x, conic.y
+    __shared__ float4 s_q1[RENDER_THREADS];   // conic.z, opacity, r, g
+    __shared__ float4 s_q2[RENDER_THREADS];   // b, thr, (list position + 1) as bits, unused
+    __shared__ uint32_t s_warp_count[RENDER_WARPS];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t tiles_x = (W + TILE_X - 1) / TILE_X;
+    const uint32_t tile_px = blockIdx.x * TILE_X, tile_py = blockIdx.y * TILE_Y;
+    int lx, ly;
+    tile_pixel(tid, lx, ly);
+    const uint32_t px = tile_px + lx, py = tile_py + ly;
+    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
+    const float pixfx = (float)px, pixfy = (float)py;
+    // pixel-centre rectangle of the part of the tile that is inside the image
+    const float rx0 = (float)tile_px, ry0 = (float)tile_py;
+    const float rx1 = (float)min(tile_px + TILE_X - 1, (uint32_t)W - 1);
+    const float ry1 = (float)min(tile_py + TILE_Y - 1, (uint32_t)H - 1);
+
+    const uint2 range = ranges[blockIdx.y * tiles_x + blockIdx.x];
+    const int total = (int)(range.y - range.x);
+    const int rounds = (total + RENDER_THREADS - 1) / RENDER_THREADS;
+
+    bool done = !inside;
+    float T = 1.0f;
+    uint32_t last_contributor = 0;
+    float C0 = 0.f, C1 = 0.f, C2 = 0.f;
+
+    for (int r = 0; r < rounds; ++r) {
+        // all pixels finished -> stop fetching (also orders the previous round's smem reads
+        // before this round's writes)
+        if (__syncthreads_count(done) == RENDER_THREADS) break;
+
+        const int progress = r * RENDER_THREADS + tid;
+        bool keep = false;
+        float4 q0, q1, q2;
+        if (progress < total) {
+            const uint32_t id = point_list[range.x + progress];
+            const GaussRec* g = rec + id;
+            q0 = __ldg(&g->q0);
+            q1 = __ldg(&g->q1);
+            q2 = __ldg(&g->q2);
+            keep = !tile_rejects(q0.x, q0.y, q0.z, q0.w, q1.x, q2.y, rx0, ry0, rx1, ry1);
+        }
+        const unsigned kmask = __ballot_sync(0xffffffffu, keep);
+        if (lane == 0) s_warp_count[warp] = __popc(kmask);
+        __syncthreads();
+        int before = 0, kept = 0;
+#pragma unroll
+        for (int w = 0; w < RENDER_WARPS; ++w) {
+            const int c = (int)s_warp_count[w];
+            if (w < warp) before += c;
+            kept += c;
+        }
+        if (keep) {
+            const int pos = before + __popc(kmask & ((1u << lane) - 1u));
+            s_q0[pos] = q0;
+            s_q1[pos] = q1;
+            s_q2[pos] = make_float4(q2.x, q2.y, __uint_as_float((uint32_t)progress + 1u), 0.f);
+        }
+        __syncthreads();
+
+        for (int j = 0; !done && j < kept; ++j) {
+            const float4 a = s_q0[j];
+            const float4 b = s_q1[j];
+            const float4 c = s_q2[j];
+            const float dx = a.x - pixfx;
+            const float dy = a.y - pixfy;
+            const float power = gauss_power(a.z, a.w, b.x, dx, dy);
+            if (power > 0.0f || power < c.y) continue;
+            const float alpha = fminf(0.99f, b.y * expf(power));
+            if (alpha < 1.0f / 255.0f) continue;
+            const float test_T = T * (1 - alpha);
+            if (test_T < 0.0001f) {
+                done = true;
+                continue;
+            }
+            C0 = __fmaf_rn(__fmul_rn(b.z, alpha), T, C0);
+            C1 = __fmaf_rn(__fmul_rn(b.w, alpha), T, C1);
+            C2 = __fmaf_rn(__fmul_rn(c.x, alpha), T, C2);
+            T = test_T;
+            last_contributor = __float_as_uint(c.z);
+        }
+    }
+
+    if (inside) {
+        const size_t pix_id = (size_t)py * W + px;
+        final_T[pix_id] = T;
+        n_contrib[pix_id] = last_contributor;
+        const size_t plane = (size_t)H * W;
+        out_color[pix_id] = __fmaf_rn(T, bg[0], C0);
+        out_color[plane + pix_id] = __fmaf_rn(T, bg[1], C1);
+        out_color[2 * plane + pix_id] = __fmaf_rn(T, bg[2], C2);
+    }
+}
+
+}  // namespace
+
+void launch_render_forward(int W, int H, const uint2* ranges, const uint32_t* point_list,
+                           const GaussRec* rec, const float* /*colors_precomp*/, const float* bg,
+                           float* final_T, uint32_t* n_contrib, float* out_color, cudaStream_t s)
+{
+    const dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1);
+    render_forward_kernel<<<grid, RENDER_THREADS, 0, s>>>(W, H, ranges, point_list, rec, bg, final_T,
+                                                         n_contrib, out_color);
+}
+
+}  // namespace bgr

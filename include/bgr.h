@@ -1,0 +1,159 @@
+/*
+ * bgr.h — C ABI of the Blackwell Gaussian rasterizer (libbgr.so, sm_100a only).
+ *
+ * This is the drop-in boundary for the reference's rasterizer core. Every entry point names the
+ * reference interface it replaces (paths relative to
+ * /root/reference/submodules/diff-gaussian-rasterization/):
+ *
+ *   bgr_forward       <- CudaRasterizer::Rasterizer::forward      cuda_rasterizer/rasterizer.h:31-54
+ *                        (called from RasterizeGaussiansCUDA,      rasterize_points.cu:35-115)
+ *   bgr_backward      <- CudaRasterizer::Rasterizer::backward     cuda_rasterizer/rasterizer.h:56-85
+ *                        (called from RasterizeGaussiansBackwardCUDA, rasterize_points.cu:117-196)
+ *   bgr_mark_visible  <- CudaRasterizer::Rasterizer::markVisible  cuda_rasterizer/rasterizer.h:24-29
+ *                        (called from markVisible,                 rasterize_points.cu:198-217)
+ *   bgr_alloc_fn      <- std::function<char*(size_t)>             cuda_rasterizer/rasterizer.h:32-34
+ *                        (resizeFunctional,                        rasterize_points.cu:27-33)
+ *
+ * Plain pointers and sizes only; no C++ types, no exceptions cross this boundary. All data
+ * pointers are DEVICE pointers to contiguous float32/int32 arrays with the reference's shapes; an
+ * absent optional input is NULL (the reference's "empty tensor => nullptr" convention,
+ * rasterize_points.cu:94-111). All work is enqueued on `stream` (a cudaStream_t passed as void*).
+ * bgr_forward synchronises that stream once to read back the number of rendered tile instances
+ * (the reference does a blocking cudaMemcpy at rasterizer_impl.cu:281).
+ *
+ * Every function returns BGR_OK (0) or a negative status; bgr_last_error() returns a
+ * thread-local human-readable message for the last failure on the calling thread.
+ */
+#ifndef BGR_H_INCLUDED
+#define BGR_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define BGR_API __attribute__((visibility("default")))
+#else
+#define BGR_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BGR_OK                 0
+#define BGR_ERR_INVALID_ARG   -1   /* bad shape / NULL where data is required              */
+#define BGR_ERR_CUDA          -2   /* a CUDA runtime call or (debug mode) a kernel failed   */
+#define BGR_ERR_ALLOC         -3   /* an allocator callback returned NULL                   */
+#define BGR_ERR_OVERFLOW      -4   /* num_rendered >= 2^31 (reference overflows silently,   */
+                                   /* rasterizer_impl.cu:280-283)                           */
+
+/* Grows (or allocates) a scratch buffer to `bytes` and returns its device address. */
+typedef void* (*bgr_alloc_fn)(size_t bytes, void* user);
+
+typedef struct BgrForwardArgs {
+    int P;                       /* number of Gaussians                                     */
+    int D;                       /* active SH degree (0..3)                                 */
+    int M;                       /* SH coefficients per channel in `shs` (0 when shs==NULL) */
+    int width, height;
+    const float* background;     /* [3]                                                     */
+    const float* means3D;        /* [P,3]                                                   */
+    const float* shs;            /* [P,M,3] or NULL                                         */
+    const float* colors_precomp; /* [P,3]   or NULL                                         */
+    const float* opacities;      /* [P]                                                     */
+    const float* scales;         /* [P,3]   or NULL                                         */
+    float        scale_modifier;
+    const float* rotations;      /* [P,4]   or NULL                                         */
+    const float* cov3D_precomp;  /* [P,6]   or NULL                                         */
+    const float* viewmatrix;     /* [16]                                                    */
+    const float* projmatrix;     /* [16]                                                    */
+    const float* cam_pos;        /* [3]                                                     */
+    float        tan_fovx, tan_fovy;
+    int          prefiltered;
+    int          debug;          /* sync + check after every stage (auxiliary.h:166-173)    */
+    float*       out_color;      /* [3,H,W]  every element is written                       */
+    int*         radii;          /* [P]      every element is written                       */
+} BgrForwardArgs;
+
+typedef struct BgrBackwardArgs {
+    int P, D, M;
+    int R;                       /* num_rendered returned by bgr_forward                    */
+    int width, height;
+    const float* background;
+    const float* means3D;
+    const float* shs;            /* or NULL */
+    const float* colors_precomp; /* or NULL */
+    const float* scales;         /* or NULL */
+    float        scale_modifier;
+    const float* rotations;      /* or NULL */
+    const float* cov3D_precomp;  /* or NULL */
+    const float* viewmatrix;
+    const float* projmatrix;
+    const float* cam_pos;
+    float        tan_fovx, tan_fovy;
+    const int*   radii;          /* [P] from forward                                        */
+    const void*  geom_buffer;    /* the three scratch buffers filled by bgr_forward         */
+    const void*  binning_buffer;
+    const void*  image_buffer;
+    const float* dL_dpix;        /* [3,H,W]                                                 */
+    void*        scratch;        /* bgr_backward_scratch_bytes(P) bytes, contents ignored   */
+    /* outputs: every element of every array is written (no pre-zeroing required)          */
+    float* dL_dmean2D;           /* [P,3] (z column = 0)                                    */
+    float* dL_dcolor;            /* [P,3]                                                   */
+    float* dL_dopacity;          /* [P]                                                     */
+    float* dL_dmean3D;           /* [P,3]                                                   */
+    float* dL_dcov3D;            /* [P,6]                                                   */
+    float* dL_dsh;               /* [P,M,3]  (may be NULL when M == 0)                      */
+    float* dL_dscale;            /* [P,3]                                                   */
+    float* dL_drot;              /* [P,4]                                                   */
+    int    debug;
+} BgrBackwardArgs;
+
+/* Forward rasterization. Writes *num_rendered (total tile instances, the reference's return
+ * value). geom/binning/image are grown through the callbacks exactly once each. */
+BGR_API int bgr_forward(const BgrForwardArgs* args,
+                bgr_alloc_fn geom_alloc, void* geom_user,
+                bgr_alloc_fn binning_alloc, void* binning_user,
+                bgr_alloc_fn image_alloc, void* image_user,
+                void* stream, int* num_rendered);
+
+BGR_API int bgr_backward(const BgrBackwardArgs* args, void* stream);
+
+/* present[i] = 1 iff Gaussian i passes the near-plane test (auxiliary.h:139-164). */
+BGR_API int bgr_mark_visible(int P, const float* means3D, const float* viewmatrix,
+                     const float* projmatrix, uint8_t* present, void* stream);
+
+/* Scratch sizes (bytes). */
+BGR_API size_t bgr_geom_bytes(int P);
+BGR_API size_t bgr_image_bytes(int width, int height);
+BGR_API size_t bgr_binning_bytes(int R);
+BGR_API size_t bgr_backward_scratch_bytes(int P);
+
+/* Introspection for the parity tests: byte offsets of the sub-arrays inside the scratch buffers.
+ * geom   : [0] records (P x 48 B: x,y,conicA,conicB | conicC,opacity,r,g | b,thr,depth,clamp bits)
+ *          [1] tiles_touched u32[P]   [2] point_offsets u32[P]   [3] control block
+ * image  : [0] final_T f32[W*H]  [1] n_contrib u32[W*H]  [2] ranges uint2[tiles]
+ * binning: [0] point_list u32[R] (sorted Gaussian ids)  [1] sorted keys u64[R]
+ *          [2] alternate keys u64[R]  [3] values a u32[R]  [4] values b u32[R]  [5] sort scratch */
+BGR_API void bgr_geom_layout(int P, size_t* offsets4);
+BGR_API void bgr_image_layout(int width, int height, size_t* offsets3);
+BGR_API void bgr_binning_layout(int R, size_t* offsets6);
+
+/* Sorting primitive on its own (used by tests and micro-benchmarks): stable LSD onesweep radix
+ * sort of n u64 keys (optionally with u32 values) on key bits [bit_lo, bit_hi).
+ * keys_a holds the input; the sorted result is returned in *keys_a or *keys_b as reported by
+ * *result_in_b. temp must hold bgr_sort_temp_bytes(n) bytes. */
+BGR_API size_t bgr_sort_temp_bytes(size_t n);
+BGR_API int bgr_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b,
+                   size_t n, int bit_lo, int bit_hi, void* temp, void* stream, int* result_in_b);
+
+/* Inclusive prefix sum of n u32 (tests). temp: bgr_scan_temp_bytes(n). */
+BGR_API size_t bgr_scan_temp_bytes(size_t n);
+BGR_API int bgr_inclusive_scan_u32(const uint32_t* in, uint32_t* out, size_t n, void* temp, void* stream);
+
+BGR_API const char* bgr_last_error(void);
+BGR_API const char* bgr_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BGR_H_INCLUDED */
