@@ -1,0 +1,298 @@
+"""Native binding: the three functions the reference exposes from its pybind module
+(``ext.cpp:15-18``), implemented over the C ABI of ``libbgr.so`` (``include/bgr.h``) with ctypes.
+
+    rasterize_gaussians(...)           <- RasterizeGaussiansCUDA          rasterize_points.cu:35-115
+    rasterize_gaussians_backward(...)  <- RasterizeGaussiansBackwardCUDA  rasterize_points.cu:117-196
+    mark_visible(...)                  <- markVisible                     rasterize_points.cu:198-217
+
+Same positional arguments, same return tuples, same "empty tensor means absent" convention.
+PyTorch is used only for device memory and the current stream. There is NO CPU fallback: if the
+shared library is missing or no CUDA device is present the import/call fails loudly.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+import torch
+
+_LIB_PATH = Path(__file__).resolve().parent / "libbgr.so"
+
+
+class _ForwardArgs(C.Structure):
+    _fields_ = [
+        ("P", C.c_int), ("D", C.c_int), ("M", C.c_int), ("width", C.c_int), ("height", C.c_int),
+        ("background", C.c_void_p), ("means3D", C.c_void_p), ("shs", C.c_void_p),
+        ("colors_precomp", C.c_void_p), ("opacities", C.c_void_p), ("scales", C.c_void_p),
+        ("scale_modifier", C.c_float), ("rotations", C.c_void_p), ("cov3D_precomp", C.c_void_p),
+        ("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p), ("cam_pos", C.c_void_p),
+        ("tan_fovx", C.c_float), ("tan_fovy", C.c_float), ("prefiltered", C.c_int),
+        ("debug", C.c_int), ("out_color", C.c_void_p), ("radii", C.c_void_p),
+    ]
+
+
+class _BackwardArgs(C.Structure):
+    _fields_ = [
+        ("P", C.c_int), ("D", C.c_int), ("M", C.c_int), ("R", C.c_int), ("width", C.c_int),
+        ("height", C.c_int), ("background", C.c_void_p), ("means3D", C.c_void_p),
+        ("shs", C.c_void_p), ("colors_precomp", C.c_void_p), ("scales", C.c_void_p),
+        ("scale_modifier", C.c_float), ("rotations", C.c_void_p), ("cov3D_precomp", C.c_void_p),
+        ("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p), ("cam_pos", C.c_void_p),
+        ("tan_fovx", C.c_float), ("tan_fovy", C.c_float), ("radii", C.c_void_p),
+        ("geom_buffer", C.c_void_p), ("binning_buffer", C.c_void_p), ("image_buffer", C.c_void_p),
+        ("dL_dpix", C.c_void_p), ("scratch", C.c_void_p), ("dL_dmean2D", C.c_void_p),
+        ("dL_dcolor", C.c_void_p), ("dL_dopacity", C.c_void_p), ("dL_dmean3D", C.c_void_p),
+        ("dL_dcov3D", C.c_void_p), ("dL_dsh", C.c_void_p), ("dL_dscale", C.c_void_p),
+        ("dL_drot", C.c_void_p), ("debug", C.c_int),
+    ]
+
+
+_ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_size_t, C.c_void_p)
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Loads libbgr.so (once). Raises if it has not been built — never falls back."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not _LIB_PATH.exists():
+        raise ImportError(
+            f"{_LIB_PATH} not found: build it with `python gaussian-splatting-own_b200/build.py` "
+            "(there is no CPU or PyTorch fallback for the rasterizer)")
+    L = C.CDLL(str(_LIB_PATH))
+    L.bgr_last_error.restype = C.c_char_p
+    L.bgr_version.restype = C.c_char_p
+    for name in ("bgr_geom_bytes", "bgr_binning_bytes", "bgr_backward_scratch_bytes"):
+        getattr(L, name).restype = C.c_size_t
+        getattr(L, name).argtypes = [C.c_int]
+    L.bgr_image_bytes.restype = C.c_size_t
+    L.bgr_image_bytes.argtypes = [C.c_int, C.c_int]
+    L.bgr_forward.restype = C.c_int
+    L.bgr_forward.argtypes = [C.POINTER(_ForwardArgs), _ALLOC_FN, C.c_void_p, _ALLOC_FN, C.c_void_p,
+                              _ALLOC_FN, C.c_void_p, C.c_void_p, C.POINTER(C.c_int)]
+    L.bgr_backward.restype = C.c_int
+    L.bgr_backward.argtypes = [C.POINTER(_BackwardArgs), C.c_void_p]
+    L.bgr_mark_visible.restype = C.c_int
+    L.bgr_mark_visible.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                   C.c_void_p]
+    L.bgr_geom_layout.argtypes = [C.c_int, C.POINTER(C.c_size_t)]
+    L.bgr_image_layout.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_size_t)]
+    L.bgr_binning_layout.argtypes = [C.c_int, C.POINTER(C.c_size_t)]
+    L.bgr_sort_temp_bytes.restype = C.c_size_t
+    L.bgr_sort_temp_bytes.argtypes = [C.c_size_t]
+    L.bgr_radix_sort.restype = C.c_int
+    L.bgr_radix_sort.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
+                                 C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.POINTER(C.c_int)]
+    L.bgr_scan_temp_bytes.restype = C.c_size_t
+    L.bgr_scan_temp_bytes.argtypes = [C.c_size_t]
+    L.bgr_inclusive_scan_u32.restype = C.c_int
+    L.bgr_inclusive_scan_u32.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
+    _lib = L
+    return L
+
+
+def _check(rc: int) -> None:
+    if rc != 0:
+        raise RuntimeError(f"bgr error {rc}: {lib().bgr_last_error().decode()}")
+
+
+def _ptr(t: torch.Tensor):
+    """Device address of a contiguous float tensor, or None (NULL) for an empty one — the
+    reference's convention for absent optional inputs (rasterize_points.cu:94-111)."""
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()
+
+
+def _f32c(t: torch.Tensor, dev) -> torch.Tensor:
+    """Contiguous f32 tensor on the compute device. Empty tensors stay as they are."""
+    if t.numel() == 0:
+        return t
+    if t.device != dev:
+        raise RuntimeError(f"expected a tensor on {dev}, got {t.device}")
+    if t.dtype != torch.float32:
+        raise RuntimeError(f"expected float32, got {t.dtype}")
+    return t.contiguous()
+
+
+def _stream(dev) -> int:
+    return torch.cuda.current_stream(dev).cuda_stream
+
+
+class _Grower:
+    """The resize-callback the core calls to size a scratch buffer (resizeFunctional,
+    rasterize_points.cu:27-33). The tensor it creates is handed back to Python."""
+
+    def __init__(self, dev):
+        self.dev = dev
+        self.tensor = torch.empty(0, dtype=torch.uint8, device=dev)
+        self.cb = _ALLOC_FN(self._grow)
+
+    def _grow(self, nbytes, _user):
+        try:
+            self.tensor = torch.empty(int(nbytes), dtype=torch.uint8, device=self.dev)
+            return self.tensor.data_ptr()
+        except Exception:  # noqa: BLE001  (reported as BGR_ERR_ALLOC by the library)
+            return None
+
+
+def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier,
+                        cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height,
+                        image_width, sh, degree, campos, prefiltered, debug):
+    """-> (num_rendered, out_color(3,H,W) f32, radii(P) i32, geomBuffer, binningBuffer, imgBuffer)"""
+    if means3D.dim() != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    if not means3D.is_cuda:
+        raise RuntimeError("the rasterizer is CUDA-only: means3D must be a CUDA tensor")
+    L = lib()
+    dev = means3D.device
+    P, H, W = int(means3D.size(0)), int(image_height), int(image_width)
+    geom, binning, img = _Grower(dev), _Grower(dev), _Grower(dev)
+    with torch.cuda.device(dev):
+        out_color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+        radii = torch.empty((P,), dtype=torch.int32, device=dev)
+        if P == 0:
+            out_color.zero_()
+            return 0, out_color, radii, geom.tensor, binning.tensor, img.tensor
+        M = int(sh.size(1)) if sh.size(0) != 0 else 0
+        keep = [_f32c(t, dev) for t in (background, means3D, sh, colors, opacity, scales, rotations,
+                                        cov3D_precomp, viewmatrix, projmatrix, campos)]
+        bg_, means_, sh_, col_, op_, sc_, rot_, cov_, view_, proj_, cam_ = keep
+        a = _ForwardArgs(
+            P=P, D=int(degree), M=M, width=W, height=H, background=_ptr(bg_), means3D=_ptr(means_),
+            shs=_ptr(sh_), colors_precomp=_ptr(col_), opacities=_ptr(op_), scales=_ptr(sc_),
+            scale_modifier=float(scale_modifier), rotations=_ptr(rot_), cov3D_precomp=_ptr(cov_),
+            viewmatrix=_ptr(view_), projmatrix=_ptr(proj_), cam_pos=_ptr(cam_),
+            tan_fovx=float(tan_fovx), tan_fovy=float(tan_fovy), prefiltered=int(bool(prefiltered)),
+            debug=int(bool(debug)), out_color=out_color.data_ptr(), radii=radii.data_ptr())
+        rendered = C.c_int(0)
+        rc = L.bgr_forward(C.byref(a), geom.cb, None, binning.cb, None, img.cb, None,
+                           _stream(dev), C.byref(rendered))
+        _check(rc)
+    return int(rendered.value), out_color, radii, geom.tensor, binning.tensor, img.tensor
+
+
+def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations,
+                                 scale_modifier, cov3D_precomp, viewmatrix, projmatrix, tan_fovx,
+                                 tan_fovy, dL_dout_color, sh, degree, campos, geomBuffer, R,
+                                 binningBuffer, imageBuffer, debug):
+    """-> (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
+    dL_drotations), shapes as rasterize_points.cu:151-159,195."""
+    L = lib()
+    dev = means3D.device
+    P = int(means3D.size(0))
+    H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
+    M = int(sh.size(1)) if sh.size(0) != 0 else 0
+    with torch.cuda.device(dev):
+        # one arena for all outputs: every element is written by the kernels, no zero fill needed
+        widths = (3, 3, 1, 3, 6, 3 * M, 3, 4)
+        arena = torch.empty((P * sum(widths),), dtype=torch.float32, device=dev)
+        parts, o = [], 0
+        for w in widths:
+            parts.append(arena[o:o + P * w])
+            o += P * w
+        dL_dmeans2D = parts[0].view(P, 3)
+        dL_dcolors = parts[1].view(P, 3)
+        dL_dopacity = parts[2].view(P, 1)
+        dL_dmeans3D = parts[3].view(P, 3)
+        dL_dcov3D = parts[4].view(P, 6)
+        dL_dsh = parts[5].view(P, M, 3)
+        dL_dscales = parts[6].view(P, 3)
+        dL_drotations = parts[7].view(P, 4)
+        if P != 0:
+            scratch = torch.empty((L.bgr_backward_scratch_bytes(P),), dtype=torch.uint8, device=dev)
+            keep = [_f32c(t, dev) for t in (background, means3D, sh, colors, scales, rotations,
+                                            cov3D_precomp, viewmatrix, projmatrix, campos,
+                                            dL_dout_color)]
+            bg_, means_, sh_, col_, sc_, rot_, cov_, view_, proj_, cam_, dpix_ = keep
+            radii_ = radii.contiguous()
+            a = _BackwardArgs(
+                P=P, D=int(degree), M=M, R=int(R), width=W, height=H, background=_ptr(bg_),
+                means3D=_ptr(means_), shs=_ptr(sh_), colors_precomp=_ptr(col_), scales=_ptr(sc_),
+                scale_modifier=float(scale_modifier), rotations=_ptr(rot_),
+                cov3D_precomp=_ptr(cov_), viewmatrix=_ptr(view_), projmatrix=_ptr(proj_),
+                cam_pos=_ptr(cam_), tan_fovx=float(tan_fovx), tan_fovy=float(tan_fovy),
+                radii=radii_.data_ptr(), geom_buffer=_ptr(geomBuffer),
+                binning_buffer=_ptr(binningBuffer), image_buffer=_ptr(imageBuffer),
+                dL_dpix=_ptr(dpix_), scratch=scratch.data_ptr(), dL_dmean2D=_ptr(dL_dmeans2D),
+                dL_dcolor=_ptr(dL_dcolors), dL_dopacity=_ptr(dL_dopacity),
+                dL_dmean3D=_ptr(dL_dmeans3D), dL_dcov3D=_ptr(dL_dcov3D), dL_dsh=_ptr(dL_dsh),
+                dL_dscale=_ptr(dL_dscales), dL_drot=_ptr(dL_drotations), debug=int(bool(debug)))
+            _check(L.bgr_backward(C.byref(a), _stream(dev)))
+            # scratch may be reused by the allocator only after the kernels that read it
+            scratch.record_stream(torch.cuda.current_stream(dev))
+    return (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
+            dL_drotations)
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    """-> bool tensor (P,), True where the Gaussian is in front of the near plane."""
+    if not means3D.is_cuda:
+        raise RuntimeError("the rasterizer is CUDA-only: means3D must be a CUDA tensor")
+    dev = means3D.device
+    P = int(means3D.size(0))
+    with torch.cuda.device(dev):
+        present = torch.zeros((P,), dtype=torch.bool, device=dev)
+        if P != 0:
+            m, v, pj = _f32c(means3D, dev), _f32c(viewmatrix, dev), _f32c(projmatrix, dev)
+            _check(lib().bgr_mark_visible(P, m.data_ptr(), v.data_ptr(), pj.data_ptr(),
+                                          present.data_ptr(), _stream(dev)))
+    return present
+
+
+# ---- introspection helpers used by the parity tests ------------------------------------------
+def geom_layout(P):
+    o = (C.c_size_t * 4)()
+    lib().bgr_geom_layout(int(P), o)
+    return dict(zip(("rec", "tiles_touched", "point_offsets", "control"), [int(x) for x in o]))
+
+
+def image_layout(W, H):
+    o = (C.c_size_t * 3)()
+    lib().bgr_image_layout(int(W), int(H), o)
+    return dict(zip(("final_T", "n_contrib", "ranges"), [int(x) for x in o]))
+
+
+def binning_layout(R):
+    o = (C.c_size_t * 6)()
+    lib().bgr_binning_layout(int(R), o)
+    return dict(zip(("point_list", "keys_a", "keys_b", "vals_a", "vals_b", "sort_temp"),
+                    [int(x) for x in o]))
+
+
+def radix_sort(keys: torch.Tensor, values: torch.Tensor | None, bit_lo: int, bit_hi: int):
+    """Stable sort of int64-viewed u64 keys (and optional int32-viewed u32 values) on key bits
+    [bit_lo, bit_hi). Returns (sorted_keys, sorted_values)."""
+    L = lib()
+    dev = keys.device
+    n = keys.numel()
+    with torch.cuda.device(dev):
+        ka = keys.contiguous().clone()
+        kb = torch.empty_like(ka)
+        va = values.contiguous().clone() if values is not None else None
+        vb = torch.empty_like(va) if va is not None else None
+        temp = torch.empty((L.bgr_sort_temp_bytes(n),), dtype=torch.uint8, device=dev)
+        in_b = C.c_int(0)
+        _check(L.bgr_radix_sort(ka.data_ptr(), kb.data_ptr(), va.data_ptr() if va is not None else None,
+                                vb.data_ptr() if vb is not None else None, n, bit_lo, bit_hi,
+                                temp.data_ptr(), _stream(dev), C.byref(in_b)))
+        torch.cuda.current_stream(dev).synchronize()
+    if in_b.value:
+        return kb, vb
+    return ka, va
+
+
+def inclusive_scan_u32(x: torch.Tensor) -> torch.Tensor:
+    L = lib()
+    dev = x.device
+    n = x.numel()
+    with torch.cuda.device(dev):
+        xin = x.contiguous()
+        out = torch.empty_like(xin)
+        temp = torch.empty((L.bgr_scan_temp_bytes(n),), dtype=torch.uint8, device=dev)
+        _check(L.bgr_inclusive_scan_u32(xin.data_ptr(), out.data_ptr(), n, temp.data_ptr(), _stream(dev)))
+        torch.cuda.current_stream(dev).synchronize()
+    return out
