@@ -116,10 +116,21 @@ __device__ __forceinline__ void tile_rect(float2 p, int max_radius, int grid_x, 
 // Rotation matrix of the (unnormalised) quaternion (r,x,y,z), listed column by column.
 __device__ __forceinline__ M3 quat_to_m3(float r, float x, float y, float z)
 {
+    // The nine entries are sums/differences of two products; which of the two products nvcc
+    // fuses into the FMA decides the last bit of the conic. Pinned to the contraction the
+    // reference build shows on sm_100a (SASS of preprocessCUDA: e.g. x*z + r*y = fma(r, y, rn(x*z)),
+    // y*y + z*z = rn(y*y) + rn(z*z)), checked bit-for-bit by the GPU parity tests.
+    const float rz = __fmul_rn(r, z), rx = __fmul_rn(r, x), xz = __fmul_rn(x, z);
+    const float yy = __fmul_rn(y, y), zz = __fmul_rn(z, z);
+    const float xy_m_rz = __fmaf_rn(x, y, -rz), xy_p_rz = __fmaf_rn(x, y, rz);
+    const float xz_p_ry = __fmaf_rn(r, y, xz), xz_m_ry = __fmaf_rn(-r, y, xz);
+    const float yz_m_rx = __fmaf_rn(y, z, -rx), yz_p_rx = __fmaf_rn(y, z, rx);
+    const float yy_zz = __fadd_rn(yy, zz);
+    const float xx_zz = __fmaf_rn(x, x, zz), xx_yy = __fmaf_rn(x, x, yy);
     return m3_cols(
-        1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
-        2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
-        2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
+        1.f - 2.f * yy_zz, 2.f * xy_m_rz, 2.f * xz_p_ry,
+        2.f * xy_p_rz, 1.f - 2.f * xx_zz, 2.f * yz_m_rx,
+        2.f * xz_m_ry, 2.f * yz_p_rx, 1.f - 2.f * xx_yy);
 }
 
 // Sigma = (S R)^T (S R); six unique entries [00,01,02,11,12,22]   (forward.cu:118-152)

@@ -93,67 +93,101 @@ __global__ void __launch_bounds__(PB_THREADS) preprocess_backward_kernel(Preproc
     }
 
     // ---- K6: conic -> cov2D -> (cov3D, T) -> J -> view-space mean -----------------------------
+    // Several terms here cancel catastrophically (denom - a*c == -b*b up to the rounding of denom,
+    // the four-term dL/dtz sum), so their value is dominated by WHICH products the reference
+    // build fuses into FMAs. To stay within 1e-4 relative of the reference's gradients the
+    // roundings below are pinned with intrinsics to the contraction observed in the reference's
+    // sm_100a SASS for computeCov2DCUDA (backward.cu:144-274); rn(.) = one IEEE rounding.
     const ProjFrame f = make_proj_frame(mean, p.focal_x, p.focal_y, p.tan_fovx, p.tan_fovy, s_view);
     const float limx = 1.3f * p.tan_fovx, limy = 1.3f * p.tan_fovy;
     const float x_grad_mul = (f.txtz < -limx || f.txtz > limx) ? 0.f : 1.f;
     const float y_grad_mul = (f.tytz < -limy || f.tytz > limy) ? 0.f : 1.f;
-    const M3 cov2D = cov2d_full(f.T, cov3D);
-    const float a = cov2D.m[0][0] + 0.3f;
-    const float b = cov2D.m[0][1];
-    const float c = cov2D.m[1][1] + 0.3f;
 
-    // t0 / t1: the two 3-vectors with cov2D = [t0.V.t0, t0.V.t1; ., t1.V.t1]
-    const V3 t0 = v3(f.T.m[0][0], f.T.m[0][1], f.T.m[0][2]);
-    const V3 t1 = v3(f.T.m[1][0], f.T.m[1][1], f.T.m[1][2]);
+    // T = W * J with J = [J00 0 J02; 0 J11 J12; 0 0 0]:
+    //   T[0][r] = fma(W2r, J02, fma(W0r, J00, rn(0 * W1r))),  T[1][r] = fma(W2r, J12, fma(0, W0r, rn(W1r * J11)))
+    const float J00 = f.J.m[0][0], J02 = f.J.m[0][2], J11 = f.J.m[1][1], J12 = f.J.m[1][2];
+    float T0[3], T1[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+        const float w0 = s_view[4 * r], w1 = s_view[4 * r + 1], w2 = s_view[4 * r + 2];
+        T0[r] = __fmaf_rn(w2, J02, __fmaf_rn(w0, J00, __fmul_rn(0.0f, w1)));
+        T1[r] = __fmaf_rn(w2, J12, __fmaf_rn(0.0f, w0, __fmul_rn(w1, J11)));
+    }
+    // S0[k] = sum_j T0[j] V[j][k], S1[k] likewise: fma(V2k, T[2], fma(V0k, T[0], rn(V1k * T[1])))
+    const float Vm[3][3] = {{cov3D[0], cov3D[1], cov3D[2]},
+                            {cov3D[1], cov3D[3], cov3D[4]},
+                            {cov3D[2], cov3D[4], cov3D[5]}};
+    float S0[3], S1[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        S0[k] = __fmaf_rn(Vm[2][k], T0[2], __fmaf_rn(Vm[0][k], T0[0], __fmul_rn(Vm[1][k], T0[1])));
+        S1[k] = __fmaf_rn(Vm[2][k], T1[2], __fmaf_rn(Vm[0][k], T1[0], __fmul_rn(Vm[1][k], T1[1])));
+    }
+    const float a = __fadd_rn(__fmaf_rn(T0[2], S0[2], __fmaf_rn(T0[1], S0[1], __fmul_rn(T0[0], S0[0]))), 0.3f);
+    const float b = __fmaf_rn(T0[2], S1[2], __fmaf_rn(T0[1], S1[1], __fmul_rn(T0[0], S1[0])));
+    const float c = __fadd_rn(__fmaf_rn(T1[2], S1[2], __fmaf_rn(T1[1], S1[1], __fmul_rn(T1[0], S1[0]))), 0.3f);
 
-    const float denom = a * c - b * b;
-    const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+    const float ac = __fmul_rn(a, c);
+    const float denom = __fmaf_rn(-b, b, ac);
+    const float denom2inv = 1.0f / __fmaf_rn(denom, denom, 0.0000001f);
     float dL_da = 0.f, dL_db = 0.f, dL_dc = 0.f;
     float dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     if (denom2inv != 0) {
-        dL_da = denom2inv * (-c * c * gcx + 2 * b * c * gcy + (denom - a * c) * gcw);
-        dL_dc = denom2inv * (-a * a * gcw + 2 * a * b * gcy + (denom - a * c) * gcx);
-        dL_db = denom2inv * 2 * (b * c * gcx - (denom + 2 * b * b) * gcy + a * b * gcw);
-        // diagonal entries of the symmetric 3D covariance, then the doubled off-diagonals
-        dcov[0] = t0.x * t0.x * dL_da + t0.x * t1.x * dL_db + t1.x * t1.x * dL_dc;
-        dcov[3] = t0.y * t0.y * dL_da + t0.y * t1.y * dL_db + t1.y * t1.y * dL_dc;
-        dcov[5] = t0.z * t0.z * dL_da + t0.z * t1.z * dL_db + t1.z * t1.z * dL_dc;
-        dcov[1] = 2 * t0.x * t0.y * dL_da + (t0.x * t1.y + t0.y * t1.x) * dL_db + 2 * t1.x * t1.y * dL_dc;
-        dcov[2] = 2 * t0.x * t0.z * dL_da + (t0.x * t1.z + t0.z * t1.x) * dL_db + 2 * t1.x * t1.z * dL_dc;
-        dcov[4] = 2 * t0.z * t0.y * dL_da + (t0.y * t1.z + t0.z * t1.y) * dL_db + 2 * t1.y * t1.z * dL_dc;
+        const float two_b = __fadd_rn(b, b), two_a = __fadd_rn(a, a);
+        const float d_m_ac = __fadd_rn(denom, -ac);                 // == -b*b up to rounding
+        const float d_p_2bb = __fmaf_rn(b, two_b, denom);
+        const float two_bc = __fmul_rn(c, two_b), two_ab = __fmul_rn(b, two_a);
+        const float bc = __fmul_rn(b, c), ab = __fmul_rn(b, a);
+        const float na = __fmaf_rn(gcw, d_m_ac, __fmaf_rn(gcy, two_bc, -__fmul_rn(gcx, __fmul_rn(c, c))));
+        const float nc = __fmaf_rn(gcx, d_m_ac, __fmaf_rn(gcy, two_ab, -__fmul_rn(gcw, __fmul_rn(a, a))));
+        const float nb = __fmaf_rn(gcw, ab, __fmaf_rn(gcx, bc, -__fmul_rn(gcy, d_p_2bb)));
+        dL_da = __fmul_rn(na, denom2inv);
+        dL_dc = __fmul_rn(nc, denom2inv);
+        dL_db = __fmul_rn(__fadd_rn(denom2inv, denom2inv), nb);
+        // diagonal: fma(dc, rn(T1k^2), fma(da, rn(T0k^2), rn(db * rn(T0k*T1k))))
+        dcov[0] = __fmaf_rn(dL_dc, __fmul_rn(T1[0], T1[0]), __fmaf_rn(dL_da, __fmul_rn(T0[0], T0[0]), __fmul_rn(dL_db, __fmul_rn(T0[0], T1[0]))));
+        dcov[3] = __fmaf_rn(dL_dc, __fmul_rn(T1[1], T1[1]), __fmaf_rn(dL_da, __fmul_rn(T0[1], T0[1]), __fmul_rn(dL_db, __fmul_rn(T0[1], T1[1]))));
+        dcov[5] = __fmaf_rn(dL_dc, __fmul_rn(T1[2], T1[2]), __fmaf_rn(dL_da, __fmul_rn(T0[2], T0[2]), __fmul_rn(dL_db, __fmul_rn(T0[2], T1[2]))));
+        // off-diagonal (doubled): fma(dc, rn(2T1i*T1j), fma(da, rn(2T0i*T0j), rn(db * fma(T0i, T1j, rn(T0j*T1i)))))
+        dcov[1] = __fmaf_rn(dL_dc, __fmul_rn(T1[1], __fadd_rn(T1[0], T1[0])),
+                            __fmaf_rn(dL_da, __fmul_rn(T0[1], __fadd_rn(T0[0], T0[0])),
+                                      __fmul_rn(dL_db, __fmaf_rn(T0[0], T1[1], __fmul_rn(T0[1], T1[0])))));
+        dcov[2] = __fmaf_rn(dL_dc, __fmul_rn(T1[2], __fadd_rn(T1[0], T1[0])),
+                            __fmaf_rn(dL_da, __fmul_rn(T0[2], __fadd_rn(T0[0], T0[0])),
+                                      __fmul_rn(dL_db, __fmaf_rn(T0[0], T1[2], __fmul_rn(T0[2], T1[0])))));
+        dcov[4] = __fmaf_rn(dL_dc, __fmul_rn(T1[2], __fadd_rn(T1[1], T1[1])),
+                            __fmaf_rn(dL_da, __fmul_rn(T0[1], __fadd_rn(T0[2], T0[2])),
+                                      __fmul_rn(dL_db, __fmaf_rn(T0[1], T1[2], __fmul_rn(T0[2], T1[1])))));
     }
 #pragma unroll
     for (int k = 0; k < 6; ++k) p.dL_dcov3D[6 * i + k] = dcov[k];
 
-    // V.t0 and V.t1 (V symmetric)
-    const V3 Vt0 = v3(cov3D[0] * t0.x + cov3D[1] * t0.y + cov3D[2] * t0.z,
-                      cov3D[1] * t0.x + cov3D[3] * t0.y + cov3D[4] * t0.z,
-                      cov3D[2] * t0.x + cov3D[4] * t0.y + cov3D[5] * t0.z);
-    const V3 Vt1 = v3(cov3D[0] * t1.x + cov3D[1] * t1.y + cov3D[2] * t1.z,
-                      cov3D[1] * t1.x + cov3D[3] * t1.y + cov3D[4] * t1.z,
-                      cov3D[2] * t1.x + cov3D[4] * t1.y + cov3D[5] * t1.z);
-    const V3 dT0 = (2 * dL_da) * Vt0 + dL_db * Vt1;
-    const V3 dT1 = (2 * dL_dc) * Vt1 + dL_db * Vt0;
-
-    // T = W * J  =>  dL/dJ[c][k] = sum_r W[k][r] * dL/dT[c][r]
-    const M3& Wm = f.W;
-    const float dL_dJ00 = Wm.m[0][0] * dT0.x + Wm.m[0][1] * dT0.y + Wm.m[0][2] * dT0.z;
-    const float dL_dJ02 = Wm.m[2][0] * dT0.x + Wm.m[2][1] * dT0.y + Wm.m[2][2] * dT0.z;
-    const float dL_dJ11 = Wm.m[1][0] * dT1.x + Wm.m[1][1] * dT1.y + Wm.m[1][2] * dT1.z;
-    const float dL_dJ12 = Wm.m[2][0] * dT1.x + Wm.m[2][1] * dT1.y + Wm.m[2][2] * dT1.z;
+    // dL/dT0k = fma(2*S0k, da, rn(S1k*db)),  dL/dT1k = fma(S0k, db, rn(2*S1k*dc))
+    float dT0[3], dT1[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        dT0[k] = __fmaf_rn(__fadd_rn(S0[k], S0[k]), dL_da, __fmul_rn(S1[k], dL_db));
+        dT1[k] = __fmaf_rn(S0[k], dL_db, __fmul_rn(__fadd_rn(S1[k], S1[k]), dL_dc));
+    }
+    // T = W * J  =>  dL/dJ[c][k] = sum_r W[k][r] dL/dT[c][r] = fma(Wk2, d2, fma(Wk0, d0, rn(Wk1 * d1)))
+    const float dL_dJ00 = __fmaf_rn(s_view[8], dT0[2], __fmaf_rn(s_view[0], dT0[0], __fmul_rn(s_view[4], dT0[1])));
+    const float dL_dJ02 = __fmaf_rn(s_view[10], dT0[2], __fmaf_rn(s_view[2], dT0[0], __fmul_rn(s_view[6], dT0[1])));
+    const float dL_dJ11 = __fmaf_rn(s_view[9], dT1[2], __fmaf_rn(s_view[1], dT1[0], __fmul_rn(s_view[5], dT1[1])));
+    const float dL_dJ12 = __fmaf_rn(s_view[10], dT1[2], __fmaf_rn(s_view[2], dT1[0], __fmul_rn(s_view[6], dT1[1])));
 
     const float tz = 1.f / f.t.z;
-    const float tz2 = tz * tz;
-    const float tz3 = tz2 * tz;
-    const float dL_dtx = x_grad_mul * -p.focal_x * tz2 * dL_dJ02;
-    const float dL_dty = y_grad_mul * -p.focal_y * tz2 * dL_dJ12;
-    const float dL_dtz = -p.focal_x * tz2 * dL_dJ00 - p.focal_y * tz2 * dL_dJ11 +
-                         (2 * p.focal_x * f.t.x) * tz3 * dL_dJ02 +
-                         (2 * p.focal_y * f.t.y) * tz3 * dL_dJ12;
-    // back through t = view * mean (rotation part transposed)
-    V3 dmean = v3(s_view[0] * dL_dtx + s_view[1] * dL_dty + s_view[2] * dL_dtz,
-                  s_view[4] * dL_dtx + s_view[5] * dL_dty + s_view[6] * dL_dtz,
-                  s_view[8] * dL_dtx + s_view[9] * dL_dty + s_view[10] * dL_dtz);
+    const float tz2 = __fmul_rn(tz, tz);
+    const float tz3 = __fmul_rn(tz2, tz);
+    const float hx = p.focal_x, hy = p.focal_y;
+    const float dL_dtx = __fmul_rn(dL_dJ02, __fmul_rn(tz2, __fmul_rn(x_grad_mul, -hx)));
+    const float dL_dty = __fmul_rn(dL_dJ12, __fmul_rn(tz2, __fmul_rn(y_grad_mul, -hy)));
+    float dL_dtz = __fmaf_rn(dL_dJ00, __fmul_rn(tz2, -hx), -__fmul_rn(dL_dJ11, __fmul_rn(tz2, hy)));
+    dL_dtz = __fmaf_rn(dL_dJ02, __fmul_rn(tz3, __fmul_rn(f.t.x, __fadd_rn(hx, hx))), dL_dtz);
+    dL_dtz = __fmaf_rn(dL_dJ12, __fmul_rn(tz3, __fmul_rn(f.t.y, __fadd_rn(hy, hy))), dL_dtz);
+    // back through t = view * mean (rotation part transposed): fma(dtz, v2, fma(dtx, v0, rn(dty * v1)))
+    V3 dmean = v3(__fmaf_rn(dL_dtz, s_view[2], __fmaf_rn(dL_dtx, s_view[0], __fmul_rn(dL_dty, s_view[1]))),
+                  __fmaf_rn(dL_dtz, s_view[6], __fmaf_rn(dL_dtx, s_view[4], __fmul_rn(dL_dty, s_view[5]))),
+                  __fmaf_rn(dL_dtz, s_view[10], __fmaf_rn(dL_dtx, s_view[8], __fmul_rn(dL_dty, s_view[9]))));
 
     // ---- K7a: screen-space mean -> 3D mean through the perspective divide ---------------------
     {

@@ -99,7 +99,11 @@ def compare(scene, cam, bg, deg, mod, label, time_it=False, dpix=None):
         dpix = synthetic.make_upstream_grad(H, W)
     g_ref = util.native_backward(ref_backend, a_ref, o_ref, dpix)
     g_new = util.native_backward(_C, a_new, o_new, dpix)
+    g_ref2 = util.native_backward(ref_backend, a_ref, o_ref, dpix)
     torch.cuda.synchronize()
+    for n_, r, m in zip(("dL_dmeans2D", "dL_dcolors", "dL_dopacity", "dL_dmeans3D", "dL_dcov3D", "dL_dsh", "dL_dscales", "dL_drotations"), g_ref, g_ref2):
+        err = (r.double() - m.double()).abs(); tol = 1e-6 + 1e-4 * r.double().abs()
+        print(f"  ref-vs-ref {n_}: max err {err.max().item() if r.numel() else 0:.3e} viol {int((err > tol).sum())} max err/tol {(err / tol).max().item() if r.numel() else 0:.2f}")
     names = ("dL_dmeans2D", "dL_dcolors", "dL_dopacity", "dL_dmeans3D", "dL_dcov3D", "dL_dsh", "dL_dscales", "dL_drotations")
     for n_, r, m in zip(names, g_ref, g_new):
         r64, m64 = r.double(), m.double()
