@@ -1,0 +1,431 @@
+#!/usr/bin/env python
+"""Benchmark of the rasterizer hot path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+One "step" = forward + backward of ONE 1920x1080 view over 3M synthetic SH-degree-3 Gaussians
+(BASELINE.json configs[2]; seeded scene of SURVEY.md §8(d)). With N > 1 ranks (torchrun) every
+rank renders its own camera over the replicated Gaussians and the 59 floats/Gaussian of leaf
+gradients are summed with ONE NCCL all-reduce issued in place on the buffer the backward kernels
+wrote (weak scaling: per-GPU work fixed).
+
+  value : views/s, inputs resident in HBM, native calls (C ABI), CUDA-event timed, max over ranks
+  e2e   : views/s through the public API (GaussianRasterizer + autograd) including per step the
+          H2D copy of the camera block and the (3,H,W) loss weights from pinned host memory and the
+          D2H read of the loss
+  --impl reference : the UNMODIFIED reference CUDA kernels (oracle/_ref/libref_rasterizer.so,
+          compiled from /root/reference by oracle/Makefile) behind the same Python glue and the
+          same harness. The reference has no CPU rasterizer, so the comparison
+          column named by north_star is its CUDA extension on the same B200; the CPU column is
+          `cpu_baseline` (the plain-C oracle port, one view of the same workload).
+
+Between timed iterations nothing is flushed explicitly: the inputs (708 MB of Gaussians) are
+far larger than the 126 MB L2, which is stated in config.l2.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+for p in (ROOT, ROOT / "gaussian-splatting-own_b200", ROOT / "tests"):
+    if str(p) not in sys.path:
+        sys.path.insert(0, str(p))
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+GRAD_FLOATS = 59  # means3D 3 + sh 48 + opacity 1 + scales 3 + rotations 4
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", choices=("ours", "reference"), default="ours")
+    ap.add_argument("--gaussians", type=int, default=3_000_000)
+    ap.add_argument("--res", choices=("800x800", "1080p", "4k"), default="1080p")
+    ap.add_argument("--skip-cpu-baseline", action="store_true")
+    ap.add_argument("--skip-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# --------------------------------------------------------------------------------------------
+# clocks: nvidia-smi sampled DURING the timed region (B200_PROFILING.md recipe)
+# --------------------------------------------------------------------------------------------
+class ClockSampler:
+    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+              "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.FIELDS}",
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:  # noqa: BLE001
+            self.proc = None
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:  # noqa: BLE001
+            self.proc.kill()
+        sm, mx, power, reasons = [], [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for line in open(self.path).read().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); power.append(float(f[3]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        os.unlink(self.path)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)),
+                "power_w_max": float(max(power)), "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# --------------------------------------------------------------------------------------------
+# workload
+# --------------------------------------------------------------------------------------------
+def load_backend(impl):
+    if impl == "ours":
+        from diff_gaussian_rasterization import _C
+        _C.lib()  # fail loudly if libbgr.so is missing: there is no fallback
+        return _C
+    from oracle import ref_backend
+    if not ref_backend.available():
+        return None
+    ref_backend.lib()
+    return ref_backend
+
+
+class Workload:
+    def __init__(self, args, rank, device):
+        import synthetic
+        self.W, self.H, focal = synthetic.RESOLUTIONS[args.res]
+        self.P = args.gaussians
+        self.cam = synthetic.make_camera(self.W, self.H, focal, view_seed=rank)
+        self.scene_cpu = synthetic.make_gaussians(self.P, seed=0)
+        self.scene = {k: v.to(device) for k, v in self.scene_cpu.items()}
+        self.bg = torch.zeros(3, device=device)
+        self.dpix_cpu = synthetic.make_upstream_grad(self.H, self.W, seed=1)
+        self.dpix = self.dpix_cpu.to(device)
+        self.device = device
+        c = self.cam
+        self.view, self.proj, self.campos = (c.viewmatrix.to(device), c.projmatrix.to(device),
+                                             c.campos.to(device))
+        self.empty = torch.Tensor([])
+
+    def fwd_args(self):
+        s, c, e = self.scene, self.cam, self.empty
+        return (self.bg, s["means3D"], e, s["opacities"], s["scales"], s["rotations"], 1.0, e,
+                self.view, self.proj, c.tanfovx, c.tanfovy, self.H, self.W, s["shs"], 3, self.campos,
+                False, False)
+
+    def bwd_args(self, out):
+        s, c, e = self.scene, self.cam, self.empty
+        R, _color, radii, geom, binning, img = out
+        return (self.bg, s["means3D"], radii, e, s["scales"], s["rotations"], 1.0, e, self.view,
+                self.proj, c.tanfovx, c.tanfovy, self.dpix, s["shs"], 3, self.campos, geom, R,
+                binning, img, False)
+
+
+def make_native_step(backend, wl, world, impl):
+    """forward + backward through the backend's `_C`-signature calls; N > 1 adds the all-reduce."""
+    import torch.distributed as dist
+
+    def step():
+        out = backend.rasterize_gaussians(*wl.fwd_args())
+        grads = backend.rasterize_gaussians_backward(*wl.bwd_args(out))
+        if world > 1:
+            if impl == "ours":
+                dist.all_reduce(backend.leaf_grad_arena(grads))       # in place, one collective
+            else:
+                for t in (grads[3], grads[5], grads[2], grads[6], grads[7]):
+                    dist.all_reduce(t)
+        return out, grads
+    return step
+
+
+def make_e2e_step(backend, wl, world, impl):
+    """The call a user makes (gaussian_renderer/__init__.py:85-93) + loss stub, with the per-step
+    host inputs (camera block, loss weights) copied from pinned memory and the loss read back."""
+    import torch.distributed as dist
+    import diff_gaussian_rasterization as dgr
+    if impl == "ours":
+        Rasterizer = dgr.GaussianRasterizer
+    else:
+        fn = dgr.make_rasterize_function(backend)
+
+        class Rasterizer(dgr.GaussianRasterizer):
+            _rasterize = staticmethod(lambda *a: fn.apply(*a))
+            _backend = backend
+    dev = wl.device
+    c = wl.cam
+    cam_host = torch.cat([c.viewmatrix.reshape(-1), c.projmatrix.reshape(-1), c.campos.reshape(-1),
+                          torch.zeros(3)]).pin_memory()
+    w_host = wl.dpix_cpu.pin_memory()
+    cam_dev = torch.empty_like(cam_host, device=dev)
+    w_dev = torch.empty_like(w_host, device=dev)
+    loss_host = torch.zeros((), dtype=torch.float32).pin_memory()
+    leaves = {k: v.clone().requires_grad_(True) for k, v in wl.scene.items()}
+    h2d = cam_host.numel() * 4 + w_host.numel() * 4
+
+    def step():
+        cam_dev.copy_(cam_host, non_blocking=True)
+        w_dev.copy_(w_host, non_blocking=True)
+        for t in leaves.values():
+            t.grad = None
+        settings = dgr.GaussianRasterizationSettings(
+            image_height=wl.H, image_width=wl.W, tanfovx=c.tanfovx, tanfovy=c.tanfovy,
+            bg=cam_dev[35:38], scale_modifier=1.0, viewmatrix=cam_dev[0:16].view(4, 4),
+            projmatrix=cam_dev[16:32].view(4, 4), sh_degree=3, campos=cam_dev[32:35],
+            prefiltered=False, debug=False)
+        means2D = torch.zeros_like(leaves["means3D"], requires_grad=True)
+        color, _radii = Rasterizer(settings)(
+            means3D=leaves["means3D"], means2D=means2D, shs=leaves["shs"], colors_precomp=None,
+            opacities=leaves["opacities"], scales=leaves["scales"], rotations=leaves["rotations"],
+            cov3D_precomp=None)
+        loss = (color * w_dev).sum()
+        loss.backward()
+        if world > 1:
+            for t in leaves.values():
+                dist.all_reduce(t.grad)
+        loss_host.copy_(loss.detach(), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return float(loss_host)
+    return step, h2d, 4
+
+
+def timed(step, steps, warmup, world, device):
+    """W warm-up steps, then exactly K steps between barrier + synchronize on both sides; CUDA
+    events on the launching (current) stream; max over ranks."""
+    import torch.distributed as dist
+    for _ in range(warmup):
+        step()
+    torch.cuda.synchronize(device)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(device)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize(device)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(device)
+    ms = torch.tensor([e0.elapsed_time(e1)], device=device, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms.item())
+
+
+# --------------------------------------------------------------------------------------------
+# roofline (SURVEY.md §8(d) algorithmic bytes / flops per unit; DESIGN.md "Measurement")
+# --------------------------------------------------------------------------------------------
+def peaks():
+    path = ROOT / "MEASURED_PEAKS.json"
+    if path.exists():
+        d = json.loads(path.read_text())
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)", float(d.get("sm_max_mhz", 1965.0))
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)", 1965.0
+
+
+def roofline_report(backend, wl, steps, device):
+    """Per-stage durations from CUDA events recorded on the launch stream inside libbgr (mean over
+    `steps` extra steps run right after the timed region, same process and inputs), combined with
+    the algorithmic bytes / flops of each stage."""
+    P, W, H = wl.P, wl.W, wl.H
+    backend.stage_timing(True)
+    acc, n = {}, 0
+    out = None
+    for _ in range(steps):
+        out = backend.rasterize_gaussians(*wl.fwd_args())
+        backend.rasterize_gaussians_backward(*wl.bwd_args(out))
+        torch.cuda.synchronize(device)
+        for k, v in backend.stage_times().items():
+            acc[k] = acc.get(k, 0.0) + v
+        n += 1
+    backend.stage_timing(False)
+    ms = {k: v / n for k, v in acc.items()}
+    R = int(out[0])
+    V = int((out[2] > 0).sum().item())
+    C = P - V
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    st = backend.render_stats(out, P, W, H)
+    il = backend.image_layout(W, H)
+    n_contrib = out[5][il["n_contrib"]:il["n_contrib"] + 4 * W * H].view(torch.int32)
+    n_pair = int(n_contrib.long().sum().item())
+    hbm_peak, peak_src, sm_mhz = peaks()
+    n_sm = torch.cuda.get_device_properties(device).multi_processor_count
+    fp32_peak = n_sm * 128 * 2 * sm_mhz * 1e6 / 1e12  # TFLOP/s at max SM clock
+    bytes_ = {
+        "preprocess": 20 * P + 291 * V,
+        "scan": 8 * P,
+        "emit_keys": 20 * V + 12 * R,
+        "radix_sort": 24 * R,
+        "tile_ranges": 8 * R + 8 * tiles,
+        "clear_accumulators": 48 * P,
+        "preprocess_backward": 555 * V + 284 * C,
+    }
+    flops = {
+        # 25 flop per pair whose exponential is evaluated (11 for pairs rejected at the power
+        # test) + 6 per blended pair; backward: the same re-evaluation + 75 per blended pair
+        "render_forward": 11 * (st["examined"] - st["exp_evaluated"]) + 25 * st["exp_evaluated"] + 6 * st["blended"],
+        "render_backward": 11 * (st["examined"] - st["exp_evaluated"]) + 25 * st["exp_evaluated"] + 75 * st["blended"],
+    }
+    stages = []
+    for name, t in ms.items():
+        if name in bytes_:
+            a = bytes_[name] / (t * 1e-3) / 1e9
+            stages.append({"kernel": name, "ms": round(t, 4), "bound": "hbm", "achieved": round(a, 1),
+                           "peak": hbm_peak, "unit": "GB/s", "frac": round(a / hbm_peak, 4),
+                           "algorithmic_bytes": bytes_[name]})
+        else:
+            a = flops[name] / (t * 1e-3) / 1e12
+            stages.append({"kernel": name, "ms": round(t, 4), "bound": "fp32", "achieved": round(a, 2),
+                           "peak": round(fp32_peak, 1), "unit": "TFLOP/s", "frac": round(a / fp32_peak, 4),
+                           "algorithmic_flops": flops[name]})
+    top = max(stages, key=lambda s: s["ms"])
+    roof = dict(top)
+    roof["traffic"] = None
+    roof["peak_source"] = peak_src if top["bound"] == "hbm" else \
+        f"{n_sm} SMs x 128 FMA lanes x 2 x {sm_mhz:.0f} MHz (no tensor-core work on this path)"
+    # the dominant HBM-bound stage, so that the line always carries one bandwidth roofline too
+    hbm = [s for s in stages if s["bound"] == "hbm"]
+    workload_stats = {"P": P, "visible": V, "num_rendered": R, "n_pair_sum_n_contrib": n_pair,
+                      "mean_tile_list": round(R / tiles, 1), **st}
+    return roof, stages, (max(hbm, key=lambda s: s["ms"]) if hbm else None), workload_stats, peak_src
+
+
+def cpu_baseline(wl):
+    """One view (forward + backward) of the SAME workload on the host cores with the plain-C
+    oracle port (the reference has no CPU rasterizer)."""
+    from oracle import cpu_oracle
+    sc = {k: v.numpy() for k, v in wl.scene_cpu.items()}
+    t0 = time.perf_counter()
+    o = cpu_oracle.forward(sc, wl.cam, np.zeros(3, np.float32), 3, 1.0)
+    t1 = time.perf_counter()
+    cpu_oracle.backward(o, wl.dpix_cpu.numpy())
+    t2 = time.perf_counter()
+    return {"value": round(1.0 / (t2 - t0), 5), "unit": "views/s", "cores": os.cpu_count(), "kind": "port",
+            "sample": f"1 view fwd+bwd of the full workload ({wl.P} Gaussians, {wl.W}x{wl.H}); "
+                      f"forward {t1 - t0:.2f} s (OpenMP, all cores), backward {t2 - t1:.2f} s "
+                      f"(render backward is single-threaded)"}
+
+
+def main():
+    args = parse_args()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world == 1 and args.gpus > 1:
+        print(f"--gpus {args.gpus} needs one rank per GPU: launch with torch.distributed.run "
+              f"--nproc-per-node {args.gpus}", file=sys.stderr)
+        sys.exit(2)
+    backend = load_backend(args.impl)
+    if backend is None:
+        if rank == 0:
+            print(json.dumps({"impl": "reference", "unavailable":
+                              "oracle/_ref/libref_rasterizer.so missing (build with `make -C oracle ref` "
+                              "where /root/reference exists)"}))
+        return
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the rasterizer has no CPU path")
+    device = torch.device("cuda", local_rank)
+    torch.cuda.set_device(device)
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+
+    wl = Workload(args, rank, device)
+    native = make_native_step(backend, wl, world, args.impl)
+
+    launches0 = backend.launch_count() if args.impl == "ours" else 0
+    native()  # first call: lazy init (pinned control block, func attributes)
+    torch.cuda.synchronize(device)
+    per_step_launches = (backend.launch_count() - launches0) if args.impl == "ours" else None
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ms_total = timed(native, args.steps, args.warmup, world, device)
+    clocks = sampler.stop() if rank == 0 else None
+    ms_per_step = ms_total / args.steps
+    value = world * 1000.0 / ms_per_step
+
+    e2e = None
+    if not args.skip_e2e:
+        e2e_step, h2d, d2h = make_e2e_step(backend, wl, world, args.impl)
+        ms_e2e = timed(e2e_step, args.steps, args.warmup, world, device) / args.steps
+        e2e = {"value": round(world * 1000.0 / ms_e2e, 3), "unit": "views/s", "ms_per_step": round(ms_e2e, 4),
+               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+               "api": "GaussianRasterizer(settings)(...) + loss.backward(); Gaussians stay resident "
+                      "(as in train.py), camera block + (3,H,W) loss weights copied from pinned memory"}
+
+    line = {
+        "metric": "train views/s (rasterizer fwd+bwd per view, 1080p, SH3)", "value": round(value, 3),
+        "unit": "views/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": round(ms_per_step, 4), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": args.impl,
+        "config": {"workload": f"{wl.P} Gaussians SH3 @ {wl.W}x{wl.H}, one camera per GPU "
+                               f"(BASELINE.json configs[2]; seeded scene of SURVEY.md 8d)",
+                   "gaussians": wl.P, "width": wl.W, "height": wl.H, "sh_degree": 3,
+                   "parallelism": f"view-batch dp{world}" + (", all-reduce of 59 floats/Gaussian" if world > 1 else ""),
+                   "l2": "no flush: per-step inputs (708 MB at 3M) exceed the 126 MB L2"},
+        "e2e": e2e, "clocks": clocks,
+    }
+    if args.impl == "ours":
+        line["gpu_launches"] = per_step_launches * args.steps
+        line["gpu_launches_per_step"] = per_step_launches
+        if world == 1:
+            roof, stages, hbm_top, stats, _ = roofline_report(backend, wl, max(3, min(args.steps, 10)), device)
+            line["roofline"] = roof
+            line["roofline_hbm"] = hbm_top
+            line["roofline_stages"] = stages
+            line["workload_stats"] = stats
+        if world == 1 and not args.skip_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(wl)
+    else:
+        line["reference"] = ("unmodified reference CUDA kernels (oracle/_ref, nvcc sm_100a) on the same GPU; "
+                             "the reference has no CPU implementation of this path")
+        line["cpu_baseline"] = {"value": line["value"], "unit": "views/s", "cores": 0, "kind": "reference",
+                                "sample": "not a CPU run: reference CUDA extension, same workload and harness"}
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

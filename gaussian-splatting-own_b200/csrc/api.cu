@@ -9,6 +9,10 @@
 #include "../../include/bgr.h"
 #include "bgr_common.cuh"
 
+namespace bgr {
+unsigned long long g_kernel_launches = 0;
+}
+
 namespace {
 
 thread_local std::string g_last_error;
@@ -48,6 +52,38 @@ bgr::GeomControl* pinned_control()
     return host;
 }
 
+// ---- diagnostics: per-stage CUDA-event timing (off by default) and a kernel-launch counter ------
+enum Stage {
+    ST_PREPROCESS = 0, ST_SCAN, ST_EMIT, ST_SORT, ST_RANGES, ST_RENDER_FWD, ST_ACC_CLEAR,
+    ST_RENDER_BWD, ST_PREPROCESS_BWD, ST_COUNT
+};
+const char* const kStageNames[ST_COUNT] = {
+    "preprocess", "scan", "emit_keys", "radix_sort", "tile_ranges", "render_forward",
+    "clear_accumulators", "render_backward", "preprocess_backward"};
+
+struct StageTimer {
+    bool on = false;
+    bool have_events = false;
+    cudaEvent_t ev[2 * ST_COUNT];
+    bool used[ST_COUNT] = {};
+    void begin(int st, cudaStream_t s)
+    {
+        if (!on) return;
+        if (!have_events) {
+            for (auto& e : ev) cudaEventCreate(&e);
+            have_events = true;
+        }
+        cudaEventRecord(ev[2 * st], s);
+    }
+    void end(int st, cudaStream_t s)
+    {
+        if (!on) return;
+        cudaEventRecord(ev[2 * st + 1], s);
+        used[st] = true;
+    }
+};
+StageTimer g_timer;
+
 bool env_flag(const char* name)
 {
     const char* v = std::getenv(name);
@@ -60,6 +96,28 @@ extern "C" {
 
 BGR_API const char* bgr_last_error(void) { return g_last_error.c_str(); }
 BGR_API const char* bgr_version(void) { return "bgr 0.1 (sm_100a)"; }
+
+BGR_API unsigned long long bgr_launch_count(void) { return bgr::g_kernel_launches; }
+
+BGR_API void bgr_stage_timing(int enable)
+{
+    g_timer.on = enable != 0;
+    for (bool& u : g_timer.used) u = false;
+}
+BGR_API int bgr_stage_count(void) { return ST_COUNT; }
+BGR_API const char* bgr_stage_name(int i) { return (i >= 0 && i < ST_COUNT) ? kStageNames[i] : ""; }
+BGR_API int bgr_stage_times(float* ms, int cap)
+{
+    int n = 0;
+    for (int i = 0; i < ST_COUNT && i < cap; ++i, ++n) {
+        ms[i] = -1.0f;
+        if (!g_timer.used[i]) continue;
+        if (cudaEventSynchronize(g_timer.ev[2 * i + 1]) != cudaSuccess) continue;
+        float t = 0.f;
+        if (cudaEventElapsedTime(&t, g_timer.ev[2 * i], g_timer.ev[2 * i + 1]) == cudaSuccess) ms[i] = t;
+    }
+    return n;
+}
 
 BGR_API size_t bgr_geom_bytes(int P) { return bgr::geom_layout((size_t)std::max(P, 0)).total; }
 BGR_API size_t bgr_image_bytes(int width, int height)
@@ -155,11 +213,15 @@ BGR_API int bgr_forward(const BgrForwardArgs* a, bgr_alloc_fn geom_alloc, void* 
     pp.tan_fovx = a->tan_fovx; pp.tan_fovy = a->tan_fovy; pp.focal_x = focal_x; pp.focal_y = focal_y;
     pp.grid_x = grid_x; pp.grid_y = grid_y; pp.prefiltered = a->prefiltered;
     pp.radii = a->radii; pp.rec = rec; pp.tiles_touched = tiles; pp.control = ctl;
+    g_timer.begin(ST_PREPROCESS, s);
     launch_preprocess(pp, s);
+    g_timer.end(ST_PREPROCESS, s);
     if ((rc = stage_check(debug, s, "preprocess"))) return rc;
 
+    g_timer.begin(ST_SCAN, s);
     launch_inclusive_scan(tiles, offsets, (size_t)a->P, scan_state, &ctl->scan_ticket,
                           &ctl->num_rendered, s);
+    g_timer.end(ST_SCAN, s);
     if ((rc = stage_check(debug, s, "scan"))) return rc;
 
     GeomControl* host = pinned_control();
@@ -207,18 +269,24 @@ BGR_API int bgr_forward(const BgrForwardArgs* a, bgr_alloc_fn geom_alloc, void* 
         uint32_t* v_in = start_in_b ? vals_b : vals_a;
         uint32_t* v_alt = start_in_b ? vals_a : vals_b;
 
+        g_timer.begin(ST_EMIT, s);
         launch_emit_keys(a->P, rec, offsets, a->radii, grid_x, grid_y, kf, k_in, v_in, s);
+        g_timer.end(ST_EMIT, s);
         if ((rc = stage_check(debug, s, "emit keys"))) return rc;
 
         int in_alt = 0;
+        g_timer.begin(ST_SORT, s);
         if (radix_sort(k_in, k_alt, v_in, v_alt, (size_t)R, kf.sort_lo, kf.sort_hi,
                        bin + BL.sort_temp, s, &in_alt) != 0)
             return fail(BGR_ERR_INVALID_ARG, "radix sort configuration rejected");
+        g_timer.end(ST_SORT, s);
         if ((rc = stage_check(debug, s, "radix sort"))) return rc;
         const uint64_t* k_sorted = in_alt ? k_alt : k_in;  // == keys_a by construction
         const uint32_t* v_sorted = in_alt ? v_alt : v_in;
 
+        g_timer.begin(ST_RANGES, s);
         launch_tile_ranges((size_t)R, k_sorted, v_sorted, kf, num_tiles, ranges, point_list, s);
+        g_timer.end(ST_RANGES, s);
         if ((rc = stage_check(debug, s, "tile ranges"))) return rc;
     } else {
         if ((rc = check_cuda(cudaMemsetAsync(ranges, 0, (size_t)num_tiles * sizeof(uint2), s),
@@ -226,8 +294,10 @@ BGR_API int bgr_forward(const BgrForwardArgs* a, bgr_alloc_fn geom_alloc, void* 
             return rc;
     }
 
+    g_timer.begin(ST_RENDER_FWD, s);
     launch_render_forward(a->width, a->height, ranges, point_list, rec, nullptr, a->background,
                           final_T, n_contrib, a->out_color, s);
+    g_timer.end(ST_RENDER_FWD, s);
     if ((rc = stage_check(debug, s, "render forward"))) return rc;
 
     *num_rendered = (int)R;
@@ -262,14 +332,18 @@ BGR_API int bgr_backward(const BgrBackwardArgs* a, void* stream_v)
     float* acc = static_cast<float*>(a->scratch);
 
     int rc;
+    g_timer.begin(ST_ACC_CLEAR, s);
     if ((rc = check_cuda(cudaMemsetAsync(acc, 0, (size_t)a->P * ACC_STRIDE * sizeof(float), s),
                          "memset accumulators")))
         return rc;
+    g_timer.end(ST_ACC_CLEAR, s);
 
     if (a->R > 0) {
         const uint32_t* point_list = reinterpret_cast<const uint32_t*>(bin + BL.point_list);
+        g_timer.begin(ST_RENDER_BWD, s);
         launch_render_backward(a->width, a->height, ranges, point_list, rec, nullptr, a->background,
                                final_T, n_contrib, a->dL_dpix, acc, s);
+        g_timer.end(ST_RENDER_BWD, s);
         if ((rc = stage_check(debug, s, "render backward"))) return rc;
     }
 
@@ -288,7 +362,9 @@ BGR_API int bgr_backward(const BgrBackwardArgs* a, void* stream_v)
     pb.dL_dscale = a->dL_dscale; pb.dL_drot = a->dL_drot;
     if (pb.shs != nullptr && pb.dL_dsh == nullptr)
         return fail(BGR_ERR_INVALID_ARG, "dL_dsh is NULL although SHs were given");
+    g_timer.begin(ST_PREPROCESS_BWD, s);
     launch_preprocess_backward(pb, s);
+    g_timer.end(ST_PREPROCESS_BWD, s);
     if ((rc = stage_check(debug, s, "preprocess backward"))) return rc;
     return BGR_OK;
 }
@@ -303,6 +379,37 @@ BGR_API int bgr_mark_visible(int P, const float* means3D, const float* viewmatri
         return fail(BGR_ERR_INVALID_ARG, "required pointer is NULL");
     bgr::launch_mark_visible(P, means3D, viewmatrix, present, s);
     return stage_check(false, s, "mark visible");
+}
+
+BGR_API int bgr_render_stats(int P, int R, int width, int height, const void* geom_buffer,
+                             const void* binning_buffer, const void* image_buffer,
+                             unsigned long long* stats4_host, void* stream_v)
+{
+    using namespace bgr;
+    cudaStream_t s = static_cast<cudaStream_t>(stream_v);
+    if (stats4_host == nullptr || P < 0 || R < 0 || width <= 0 || height <= 0)
+        return fail(BGR_ERR_INVALID_ARG, "bad argument");
+    for (int i = 0; i < 4; ++i) stats4_host[i] = 0;
+    if (P == 0 || R == 0) return BGR_OK;
+    if (geom_buffer == nullptr || binning_buffer == nullptr || image_buffer == nullptr)
+        return fail(BGR_ERR_INVALID_ARG, "required pointer is NULL");
+    const GeomLayout GL = geom_layout((size_t)P);
+    const ImageLayout IL = image_layout((size_t)width, (size_t)height);
+    const BinningLayout BL = binning_layout((size_t)R);
+    const unsigned char* geom = static_cast<const unsigned char*>(geom_buffer);
+    const unsigned char* img = static_cast<const unsigned char*>(image_buffer);
+    const unsigned char* bin = static_cast<const unsigned char*>(binning_buffer);
+    unsigned long long* dev = nullptr;
+    int rc;
+    if ((rc = check_cuda(cudaMalloc(reinterpret_cast<void**>(&dev), 4 * sizeof(unsigned long long)), "cudaMalloc"))) return rc;
+    cudaMemsetAsync(dev, 0, 4 * sizeof(unsigned long long), s);
+    launch_render_stats(width, height, reinterpret_cast<const uint2*>(img + IL.ranges),
+                        reinterpret_cast<const uint32_t*>(bin + BL.point_list),
+                        reinterpret_cast<const GaussRec*>(geom + GL.rec), dev, s);
+    cudaMemcpyAsync(stats4_host, dev, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s);
+    rc = check_cuda(cudaStreamSynchronize(s), "render stats");
+    cudaFree(dev);
+    return rc;
 }
 
 BGR_API size_t bgr_sort_temp_bytes(size_t n) { return bgr::sort_temp_layout(n).total; }

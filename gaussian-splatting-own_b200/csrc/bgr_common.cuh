@@ -43,6 +43,9 @@ struct BinningLayout {
     size_t point_list, keys_a, keys_b, vals_a, vals_b, sort_temp, total;
 };
 
+// Number of kernels this library has launched (diagnostic; bumped by every launch_* wrapper).
+extern unsigned long long g_kernel_launches;
+
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 constexpr int SCAN_THREADS = 256;
@@ -178,6 +181,8 @@ int  radix_sort_passes(int bit_lo, int bit_hi);
 void launch_render_forward(int W, int H, const uint2* ranges, const uint32_t* point_list,
                            const GaussRec* rec, const float* colors_precomp, const float* bg,
                            float* final_T, uint32_t* n_contrib, float* out_color, cudaStream_t s);
+void launch_render_stats(int W, int H, const uint2* ranges, const uint32_t* point_list,
+                         const GaussRec* rec, unsigned long long* stats, cudaStream_t s);
 void launch_render_backward(int W, int H, const uint2* ranges, const uint32_t* point_list,
                             const GaussRec* rec, const float* colors_precomp, const float* bg,
                             const float* final_T, const uint32_t* n_contrib, const float* dL_dpix,

@@ -192,6 +192,7 @@ void launch_inclusive_scan(const uint32_t* in, uint32_t* out, size_t n, uint64_t
 {
     if (n == 0) return;
     const unsigned blocks = (unsigned)((n + SCAN_TILE - 1) / SCAN_TILE);
+    ++g_kernel_launches;
     scan_kernel<<<blocks, SCAN_THREADS, 0, s>>>(in, out, n, state, ticket, total_out);
 }
 
@@ -200,6 +201,7 @@ void launch_emit_keys(int P, const GaussRec* rec, const uint32_t* offsets, const
                       cudaStream_t s)
 {
     if (P <= 0) return;
+    ++g_kernel_launches;
     emit_keys_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, rec, offsets, radii, grid_x, grid_y, kf,
                                                     keys, vals);
 }
@@ -209,6 +211,7 @@ void launch_tile_ranges(size_t R, const uint64_t* keys_sorted, const uint32_t* v
                         cudaStream_t s)
 {
     if (R == 0) return;
+    ++g_kernel_launches;
     tile_ranges_kernel<<<(unsigned)((R + 255) / 256), 256, 0, s>>>(
         (uint32_t)R, keys_sorted, vals_sorted, kf, num_tiles, ranges, point_list);
 }

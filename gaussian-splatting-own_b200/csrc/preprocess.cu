@@ -196,6 +196,7 @@ void launch_preprocess(const PreprocessParams& p, cudaStream_t s)
     if (p.P <= 0) return;
     const int blocks = (p.P + PRE_THREADS - 1) / PRE_THREADS;
     const bool vec = p.shs != nullptr && p.M == 16 && (reinterpret_cast<uintptr_t>(p.shs) & 15) == 0;
+    ++g_kernel_launches;
     if (vec)
         preprocess_kernel<true><<<blocks, PRE_THREADS, 0, s>>>(p);
     else
@@ -206,6 +207,7 @@ void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, u
                          cudaStream_t s)
 {
     if (P <= 0) return;
+    ++g_kernel_launches;
     mark_visible_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, means3D, viewmatrix, present);
 }
 

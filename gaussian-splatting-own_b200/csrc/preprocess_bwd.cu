@@ -370,6 +370,7 @@ void launch_preprocess_backward(const PreprocessBackwardParams& p, cudaStream_t 
     const bool vec = p.shs != nullptr && p.M == 16 &&
                      (reinterpret_cast<uintptr_t>(p.shs) & 15) == 0 &&
                      (reinterpret_cast<uintptr_t>(p.dL_dsh) & 15) == 0;
+    ++g_kernel_launches;
     if (vec)
         preprocess_backward_kernel<true><<<blocks, PB_THREADS, 0, s>>>(p);
     else

@@ -231,7 +231,9 @@ int radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* v
     }
 
     const unsigned hist_blocks = (unsigned)std::min<size_t>((n + 255) / 256, 148 * 8);
+    ++g_kernel_launches;
     sort_hist_kernel<<<hist_blocks, 256, 0, s>>>(keys_a, (uint32_t)n, bit_lo, bit_hi, npasses, hist);
+    ++g_kernel_launches;
     sort_bases_kernel<<<npasses, RADIX, 0, s>>>(hist);
 
     uint64_t* kin = keys_a;
@@ -243,6 +245,7 @@ int radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* v
         const int nb = std::min(RADIX_BITS, bit_hi - shift);
         const uint32_t mask = (1u << nb) - 1u;
         uint32_t* st = status + (size_t)p * L.nblocks * RADIX;
+        ++g_kernel_launches;
         if (pairs)
             onesweep_kernel<true><<<(unsigned)L.nblocks, SORT_THREADS, onesweep_smem(true), s>>>(
                 kin, kout, vin, vout, (uint32_t)n, shift, mask, hist + p * RADIX, st, tickets + p);

@@ -204,6 +204,7 @@ void launch_render_backward(int W, int H, const uint2* ranges, const uint32_t* p
                             float* acc, cudaStream_t s)
 {
     const dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1);
+    ++g_kernel_launches;
     render_backward_kernel<<<grid, RENDER_THREADS, 0, s>>>(W, H, ranges, point_list, rec, bg, final_T,
                                                           n_contrib, dL_dpix, acc);
 }

@@ -19,12 +19,20 @@ namespace bgr {
 
 namespace {
 
+// kStats: diagnostic instantiation used by bgr_render_stats (never by bgr_forward). It runs the
+// identical traversal and additionally counts, over the whole image,
+//   stats[0] staged (tile, splat) entries that survived the tile rejection,
+//   stats[1] (pixel, splat) pairs examined (power evaluated),
+//   stats[2] pairs whose expf was evaluated,  stats[3] pairs blended into the pixel.
+template <bool kStats>
 __global__ void __launch_bounds__(RENDER_THREADS)
 render_forward_kernel(int W, int H, const uint2* __restrict__ ranges,
                       const uint32_t* __restrict__ point_list, const GaussRec* __restrict__ rec,
                       const float* __restrict__ bg, float* __restrict__ final_T,
-                      uint32_t* __restrict__ n_contrib, float* __restrict__ out_color)
+                      uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
+                      unsigned long long* __restrict__ stats)
 {
+    unsigned long long st_kept = 0, st_exam = 0, st_exp = 0, st_blend = 0;
     __shared__ float4 s_q0[RENDER_THREADS];   // x, y, conic.x, conic.y
     __shared__ float4 s_q1[RENDER_THREADS];   // conic.z, opacity, r, g
     __shared__ float4 s_q2[RENDER_THREADS];   // b, thr, (list position + 1) as bits, unused
@@ -85,6 +93,7 @@ render_forward_kernel(int W, int H, const uint2* __restrict__ ranges,
             s_q2[pos] = make_float4(q2.x, q2.y, __uint_as_float((uint32_t)progress + 1u), 0.f);
         }
         __syncthreads();
+        if (kStats && tid == 0) st_kept += (unsigned long long)kept;
 
         for (int j = 0; !done && j < kept; ++j) {
             const float4 a = s_q0[j];
@@ -93,8 +102,10 @@ render_forward_kernel(int W, int H, const uint2* __restrict__ ranges,
             const float dx = a.x - pixfx;
             const float dy = a.y - pixfy;
             const float power = gauss_power(a.z, a.w, b.x, dx, dy);
+            if (kStats) ++st_exam;
             if (power > 0.0f || power < c.y) continue;
             const float alpha = fminf(0.99f, b.y * expf(power));
+            if (kStats) ++st_exp;
             if (alpha < 1.0f / 255.0f) continue;
             const float test_T = T * (1 - alpha);
             if (test_T < 0.0001f) {
@@ -106,7 +117,16 @@ render_forward_kernel(int W, int H, const uint2* __restrict__ ranges,
             C2 = __fmaf_rn(__fmul_rn(c.x, alpha), T, C2);
             T = test_T;
             last_contributor = __float_as_uint(c.z);
+            if (kStats) ++st_blend;
         }
+    }
+
+    if (kStats) {
+        atomicAdd(&stats[0], st_kept);
+        atomicAdd(&stats[1], st_exam);
+        atomicAdd(&stats[2], st_exp);
+        atomicAdd(&stats[3], st_blend);
+        return;  // statistics only: the image buffers are not written
     }
 
     if (inside) {
@@ -127,8 +147,18 @@ void launch_render_forward(int W, int H, const uint2* ranges, const uint32_t* po
                            float* final_T, uint32_t* n_contrib, float* out_color, cudaStream_t s)
 {
     const dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1);
-    render_forward_kernel<<<grid, RENDER_THREADS, 0, s>>>(W, H, ranges, point_list, rec, bg, final_T,
-                                                         n_contrib, out_color);
+    ++g_kernel_launches;
+    render_forward_kernel<false><<<grid, RENDER_THREADS, 0, s>>>(W, H, ranges, point_list, rec, bg,
+                                                                final_T, n_contrib, out_color,
+                                                                nullptr);
+}
+
+void launch_render_stats(int W, int H, const uint2* ranges, const uint32_t* point_list,
+                         const GaussRec* rec, unsigned long long* stats, cudaStream_t s)
+{
+    const dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1);
+    render_forward_kernel<true><<<grid, RENDER_THREADS, 0, s>>>(W, H, ranges, point_list, rec, nullptr,
+                                                               nullptr, nullptr, nullptr, stats);
 }
 
 }  // namespace bgr

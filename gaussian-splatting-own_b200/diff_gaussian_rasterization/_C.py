@@ -90,6 +90,18 @@ def lib() -> C.CDLL:
     L.bgr_scan_temp_bytes.argtypes = [C.c_size_t]
     L.bgr_inclusive_scan_u32.restype = C.c_int
     L.bgr_inclusive_scan_u32.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
+    L.bgr_launch_count.restype = C.c_ulonglong
+    L.bgr_launch_count.argtypes = []
+    L.bgr_stage_timing.restype = None
+    L.bgr_stage_timing.argtypes = [C.c_int]
+    L.bgr_stage_count.restype = C.c_int
+    L.bgr_stage_name.restype = C.c_char_p
+    L.bgr_stage_name.argtypes = [C.c_int]
+    L.bgr_stage_times.restype = C.c_int
+    L.bgr_stage_times.argtypes = [C.POINTER(C.c_float), C.c_int]
+    L.bgr_render_stats.restype = C.c_int
+    L.bgr_render_stats.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                   C.c_void_p, C.POINTER(C.c_ulonglong), C.c_void_p]
     _lib = L
     return L
 
@@ -124,19 +136,30 @@ def _stream(dev) -> int:
 
 class _Grower:
     """The resize-callback the core calls to size a scratch buffer (resizeFunctional,
-    rasterize_points.cu:27-33). The tensor it creates is handed back to Python."""
+    rasterize_points.cu:27-33). The tensor it creates is handed back to Python.
+
+    The ctypes callback closes over a plain list, not over `self`: a bound-method callback would
+    form a reference cycle (self -> cb -> self) and keep hundreds of MB of scratch alive until the
+    cyclic GC runs, forcing a fresh cudaMalloc on every call."""
+
+    __slots__ = ("box", "cb")
 
     def __init__(self, dev):
-        self.dev = dev
-        self.tensor = torch.empty(0, dtype=torch.uint8, device=dev)
-        self.cb = _ALLOC_FN(self._grow)
+        box = [torch.empty(0, dtype=torch.uint8, device=dev)]
 
-    def _grow(self, nbytes, _user):
-        try:
-            self.tensor = torch.empty(int(nbytes), dtype=torch.uint8, device=self.dev)
-            return self.tensor.data_ptr()
-        except Exception:  # noqa: BLE001  (reported as BGR_ERR_ALLOC by the library)
-            return None
+        def grow(nbytes, _user):
+            try:
+                box[0] = torch.empty(int(nbytes), dtype=torch.uint8, device=dev)
+                return box[0].data_ptr()
+            except Exception:  # noqa: BLE001  (reported as BGR_ERR_ALLOC by the library)
+                return None
+
+        self.box = box
+        self.cb = _ALLOC_FN(grow)
+
+    @property
+    def tensor(self):
+        return self.box[0]
 
 
 def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier,
@@ -187,8 +210,12 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
     M = int(sh.size(1)) if sh.size(0) != 0 else 0
     with torch.cuda.device(dev):
-        # one arena for all outputs: every element is written by the kernels, no zero fill needed
-        widths = (3, 3, 1, 3, 6, 3 * M, 3, 4)
+        # One arena for all outputs: every element is written by the kernels, so no zero fill is
+        # needed. Layout: [means2D | colors | cov3D || means3D | sh | opacity | scales | rotations];
+        # the part after || is what a trainer's leaves receive (59 floats per Gaussian at M=16)
+        # and is contiguous so that a data-parallel caller can all-reduce it in place with one
+        # collective (leaf_grad_arena below) — the kernels write straight into the send buffer.
+        widths = (3, 3, 6, 3, 3 * M, 1, 3, 4)
         arena = torch.empty((P * sum(widths),), dtype=torch.float32, device=dev)
         parts, o = [], 0
         for w in widths:
@@ -196,10 +223,10 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
             o += P * w
         dL_dmeans2D = parts[0].view(P, 3)
         dL_dcolors = parts[1].view(P, 3)
-        dL_dopacity = parts[2].view(P, 1)
+        dL_dcov3D = parts[2].view(P, 6)
         dL_dmeans3D = parts[3].view(P, 3)
-        dL_dcov3D = parts[4].view(P, 6)
-        dL_dsh = parts[5].view(P, M, 3)
+        dL_dsh = parts[4].view(P, M, 3)
+        dL_dopacity = parts[5].view(P, 1)
         dL_dscales = parts[6].view(P, 3)
         dL_drotations = parts[7].view(P, 4)
         if P != 0:
@@ -241,6 +268,46 @@ def mark_visible(means3D, viewmatrix, projmatrix):
             _check(lib().bgr_mark_visible(P, m.data_ptr(), v.data_ptr(), pj.data_ptr(),
                                           present.data_ptr(), _stream(dev)))
     return present
+
+
+def leaf_grad_arena(grads) -> torch.Tensor:
+    """The flat f32 tensor that aliases (dL_dmeans3D, dL_dsh, dL_dopacity, dL_dscales,
+    dL_drotations) of one rasterize_gaussians_backward result, in that order."""
+    dL_dmeans3D, dL_dsh = grads[3], grads[5]
+    arena = dL_dmeans3D._base
+    P = dL_dmeans3D.size(0)
+    start = 12 * P
+    n = P * (3 + 3 * dL_dsh.size(1) + 1 + 3 + 4)
+    flat = arena[start:start + n]
+    assert flat.data_ptr() == dL_dmeans3D.data_ptr()
+    return flat
+
+
+# ---- diagnostics -------------------------------------------------------------------------------
+def launch_count() -> int:
+    return int(lib().bgr_launch_count())
+
+
+def stage_timing(enable: bool) -> None:
+    lib().bgr_stage_timing(int(bool(enable)))
+
+
+def stage_times() -> dict:
+    L = lib()
+    n = L.bgr_stage_count()
+    buf = (C.c_float * n)()
+    L.bgr_stage_times(buf, n)
+    return {L.bgr_stage_name(i).decode(): float(buf[i]) for i in range(n) if buf[i] >= 0}
+
+
+def render_stats(fwd_out, P, W, H) -> dict:
+    R, _c, _r, geom, binning, img = fwd_out
+    out = (C.c_ulonglong * 4)()
+    dev = geom.device
+    with torch.cuda.device(dev):
+        _check(lib().bgr_render_stats(int(P), int(R), int(W), int(H), _ptr(geom), _ptr(binning),
+                                      _ptr(img), out, _stream(dev)))
+    return dict(zip(("staged", "examined", "exp_evaluated", "blended"), [int(x) for x in out]))
 
 
 # ---- introspection helpers used by the parity tests ------------------------------------------

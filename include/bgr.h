@@ -150,6 +150,22 @@ BGR_API int bgr_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a,
 BGR_API size_t bgr_scan_temp_bytes(size_t n);
 BGR_API int bgr_inclusive_scan_u32(const uint32_t* in, uint32_t* out, size_t n, void* temp, void* stream);
 
+/* ---- diagnostics (bench.py / tests; nothing here is on the product path) --------------------- */
+/* Total number of CUDA kernels this library has launched in this process. */
+BGR_API unsigned long long bgr_launch_count(void);
+/* Per-stage CUDA-event timing on the launch stream: enable, run bgr_forward / bgr_backward, then
+ * read the durations (ms; -1 for a stage that did not run). Stage i is named bgr_stage_name(i). */
+BGR_API void bgr_stage_timing(int enable);
+BGR_API int bgr_stage_count(void);
+BGR_API const char* bgr_stage_name(int i);
+BGR_API int bgr_stage_times(float* ms, int cap);
+/* Re-traverses the forward compositing of a finished bgr_forward (its three buffers) and counts
+ * stats4_host[0] staged (tile, splat) entries, [1] (pixel, splat) pairs examined, [2] pairs whose
+ * exponential was evaluated, [3] pairs blended. Synchronises the stream. */
+BGR_API int bgr_render_stats(int P, int R, int width, int height, const void* geom_buffer,
+                             const void* binning_buffer, const void* image_buffer,
+                             unsigned long long* stats4_host, void* stream);
+
 BGR_API const char* bgr_last_error(void);
 BGR_API const char* bgr_version(void);
 

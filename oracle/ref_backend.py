@@ -55,15 +55,19 @@ def _p(t):
 
 
 class _Resizer:
-    """resizeFunctional (rasterize_points.cu:27-33): t.resize_({N}); return t.data_ptr()."""
+    """resizeFunctional (rasterize_points.cu:27-33): t.resize_({N}); return t.data_ptr().
+    The callback closes over the tensor only (no self reference => no reference cycle, the
+    buffers are released by refcount exactly as the reference's pybind module releases them)."""
 
     def __init__(self):
-        self.t = torch.empty(0, dtype=torch.uint8, device="cuda")
-        self.cb = _ALLOC_FN(self._f)
+        t = torch.empty(0, dtype=torch.uint8, device="cuda")
 
-    def _f(self, n, _u):
-        self.t.resize_(int(n))
-        return self.t.data_ptr()
+        def f(n, _u):
+            t.resize_(int(n))
+            return t.data_ptr()
+
+        self.t = t
+        self.cb = _ALLOC_FN(f)
 
 
 def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier,

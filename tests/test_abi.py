@@ -1,0 +1,130 @@
+"""CPU suite: the C-ABI library loads and exports exactly what include/bgr.h declares, the pure
+host entry points behave, and the Python drop-in surface mirrors the reference's
+(diff_gaussian_rasterization/__init__.py:157-220). No compute call is made here (no GPU)."""
+import ctypes as C
+import inspect
+import re
+from pathlib import Path
+
+import pytest
+import torch
+
+ROOT = Path(__file__).resolve().parents[1]
+HEADER = ROOT / "include" / "bgr.h"
+
+
+@pytest.fixture(scope="module")
+def lib():
+    from diff_gaussian_rasterization import _C
+    return _C.lib()
+
+
+def declared_symbols():
+    text = HEADER.read_text()
+    return sorted(set(re.findall(r"BGR_API\s+[\w\s\*]+?\b(bgr_\w+)\s*\(", text)))
+
+
+def test_header_declares_the_reference_entry_points():
+    syms = declared_symbols()
+    for s in ("bgr_forward", "bgr_backward", "bgr_mark_visible", "bgr_last_error"):
+        assert s in syms
+    assert len(syms) >= 15
+
+
+def test_library_exports_every_declared_symbol(lib):
+    for s in declared_symbols():
+        assert hasattr(lib, s), f"libbgr.so does not export {s}"
+
+
+def test_host_only_entry_points(lib):
+    assert b"sm_100a" in lib.bgr_version()
+    assert lib.bgr_geom_bytes(0) >= 0
+    g1, g2 = lib.bgr_geom_bytes(1000), lib.bgr_geom_bytes(2000)
+    assert g2 > g1 >= 1000 * 56          # 48 B record + tiles + offsets per Gaussian
+    assert lib.bgr_image_bytes(1920, 1080) >= 1920 * 1080 * 8 + 8160 * 8
+    assert lib.bgr_binning_bytes(1 << 20) >= (1 << 20) * 28
+    assert lib.bgr_backward_scratch_bytes(1000) >= 1000 * 48
+    off = (C.c_size_t * 4)()
+    lib.bgr_geom_layout(1000, off)
+    assert list(off) == sorted(off) and off[0] == 0 and all(o % 256 == 0 for o in off)
+    off3 = (C.c_size_t * 3)()
+    lib.bgr_image_layout(800, 800, off3)
+    assert off3[1] - off3[0] >= 800 * 800 * 4
+    off6 = (C.c_size_t * 6)()
+    lib.bgr_binning_layout(12345, off6)
+    assert list(off6) == sorted(off6)
+    assert lib.bgr_sort_temp_bytes(1 << 20) > 0 and lib.bgr_scan_temp_bytes(1 << 20) > 0
+
+
+def test_invalid_arguments_are_rejected_without_a_gpu(lib):
+    from diff_gaussian_rasterization import _C
+    n = C.c_int(0)
+    cb = _C._ALLOC_FN(lambda nbytes, user: None)
+    assert lib.bgr_forward(None, cb, None, cb, None, cb, None, None, C.byref(n)) == -1
+    assert b"null" in lib.bgr_last_error()
+    assert lib.bgr_backward(None, None) == -1
+    assert lib.bgr_mark_visible(-1, None, None, None, None, None) == -1
+
+
+def test_python_surface_matches_reference_names():
+    import diff_gaussian_rasterization as d
+    for name in ("GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians",
+                 "_RasterizeGaussians", "cpu_deep_copy_tuple", "_C"):
+        assert hasattr(d, name)
+    assert d.GaussianRasterizationSettings._fields == (
+        "image_height", "image_width", "tanfovx", "tanfovy", "bg", "scale_modifier", "viewmatrix",
+        "projmatrix", "sh_degree", "campos", "prefiltered", "debug")
+    sig = inspect.signature(d.GaussianRasterizer.forward)
+    assert list(sig.parameters) == ["self", "means3D", "means2D", "opacities", "shs",
+                                    "colors_precomp", "scales", "rotations", "cov3D_precomp"]
+    # the three native functions with the reference's positional arity (ext.cpp:15-18)
+    assert len(inspect.signature(d._C.rasterize_gaussians).parameters) == 19
+    assert len(inspect.signature(d._C.rasterize_gaussians_backward).parameters) == 21
+    assert len(inspect.signature(d._C.mark_visible).parameters) == 3
+    assert issubclass(d._RasterizeGaussians, torch.autograd.Function)
+
+
+def _settings(d):
+    return d.GaussianRasterizationSettings(16, 16, 1.0, 1.0, torch.zeros(3), 1.0, torch.eye(4),
+                                           torch.eye(4), 3, torch.zeros(3), False, False)
+
+
+def test_input_mode_validation_messages():
+    """Same exceptions, same (misspelt) text as the reference (__init__.py:191-195)."""
+    import diff_gaussian_rasterization as d
+    r = d.GaussianRasterizer(_settings(d))
+    m, o = torch.zeros(4, 3), torch.zeros(4, 1)
+    sh, col = torch.zeros(4, 16, 3), torch.zeros(4, 3)
+    sc, rot, cov = torch.ones(4, 3), torch.zeros(4, 4), torch.zeros(4, 6)
+    with pytest.raises(Exception, match="excatly one of either SHs or precomputed colors"):
+        r(m, m, o, shs=sh, colors_precomp=col, scales=sc, rotations=rot)
+    with pytest.raises(Exception, match="excatly one of either SHs or precomputed colors"):
+        r(m, m, o, scales=sc, rotations=rot)
+    with pytest.raises(Exception, match="exactly one of either scale/rotation pair"):
+        r(m, m, o, shs=sh, scales=sc, rotations=rot, cov3D_precomp=cov)
+    with pytest.raises(Exception, match="exactly one of either scale/rotation pair"):
+        r(m, m, o, shs=sh, scales=sc)
+    with pytest.raises(Exception, match="exactly one of either scale/rotation pair"):
+        r(m, m, o, shs=sh)
+
+
+def test_no_cpu_fallback():
+    """CPU tensors must fail loudly: the product has no CPU or eager-PyTorch path."""
+    import diff_gaussian_rasterization as d
+    r = d.GaussianRasterizer(_settings(d))
+    m, o = torch.zeros(4, 3), torch.zeros(4, 1)
+    with pytest.raises(RuntimeError, match="CUDA-only"):
+        r(m, m, o, shs=torch.zeros(4, 16, 3), scales=torch.ones(4, 3), rotations=torch.zeros(4, 4))
+    with pytest.raises(RuntimeError, match="CUDA-only"):
+        r.markVisible(m)
+    with pytest.raises(RuntimeError, match="num_points, 3"):
+        d._C.rasterize_gaussians(torch.zeros(3), torch.zeros(4, 2), *([torch.Tensor([])] * 17))
+
+
+def test_product_never_imports_the_oracle():
+    """The product path must not import, load or link anything under oracle/."""
+    pkg = ROOT / "gaussian-splatting-own_b200"
+    pat = re.compile(r"^\s*(from|import)\s+oracle\b|liboracle|libref_rasterizer|cpu_oracle|"
+                     r"#include\s+\"[^\"]*oracle", re.M)
+    for f in list(pkg.rglob("*.py")) + list(pkg.rglob("*.cu")) + list(pkg.rglob("*.cuh")):
+        assert not pat.search(f.read_text()), f"{f} reaches into oracle/"
