@@ -159,13 +159,16 @@ class Workload:
 def make_native_step(backend, wl, world, impl):
     """forward + backward through the backend's `_C`-signature calls; N > 1 adds the all-reduce."""
     import torch.distributed as dist
+    import view_parallel as vp
 
     def step():
         out = backend.rasterize_gaussians(*wl.fwd_args())
         grads = backend.rasterize_gaussians_backward(*wl.bwd_args(out))
         if world > 1:
             if impl == "ours":
-                dist.all_reduce(backend.leaf_grad_arena(grads))       # in place, one collective
+                flat, aliased = vp.flat_leaf_gradients(grads)         # zero-copy view of the arena
+                assert aliased
+                dist.all_reduce(flat)                                 # in place, one collective
             else:
                 for t in (grads[3], grads[5], grads[2], grads[6], grads[7]):
                     dist.all_reduce(t)

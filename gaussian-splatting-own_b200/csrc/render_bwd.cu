@@ -27,9 +27,9 @@ render_backward_kernel(int W, int H, const uint2* __restrict__ ranges,
                        const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix,
                        float* __restrict__ acc)
 {
-    __shared__ float4 s_q0[RENDER_THREADS];   // x, y, conic.x, conic.y
-    __shared__ float4 s_q1[RENDER_THREADS];   // conic.z, opacity, r, g
-    __shared__ float4 s_q2[RENDER_THREADS];   // b, thr, list position (bits), Gaussian id (bits)
+    __shared__ float4 s_geo[RENDER_THREADS];  // x, y, conic.x, conic.y
+    __shared__ float4 s_opa[RENDER_THREADS];  // conic.z, thr, opacity, list position (bits)
+    __shared__ float4 s_col[RENDER_THREADS];  // r, g, b, Gaussian id (bits)
     __shared__ uint32_t s_warp_count[RENDER_WARPS];
     __shared__ uint32_t s_warp_max[RENDER_WARPS];
 
@@ -45,6 +45,10 @@ render_backward_kernel(int W, int H, const uint2* __restrict__ ranges,
     const float rx0 = (float)tile_px, ry0 = (float)tile_py;
     const float rx1 = (float)min(tile_px + TILE_X - 1, (uint32_t)W - 1);
     const float ry1 = (float)min(tile_py + TILE_Y - 1, (uint32_t)H - 1);
+    const uint32_t wpx = tile_px + ((warp & 1) << 3), wpy = tile_py + ((warp >> 1) << 2);
+    const float wx0 = (float)wpx, wy0 = (float)wpy;
+    const float wx1 = (float)min(wpx + 7, (uint32_t)W - 1);
+    const float wy1 = (float)min(wpy + 3, (uint32_t)H - 1);
 
     const uint2 range = ranges[blockIdx.y * tiles_x + blockIdx.x];
 
@@ -105,27 +109,45 @@ render_backward_kernel(int W, int H, const uint2* __restrict__ ranges,
         }
         if (keep) {
             const int pos = before + __popc(kmask & ((1u << lane) - 1u));
-            s_q0[pos] = q0;
-            s_q1[pos] = q1;
-            s_q2[pos] = make_float4(q2.x, q2.y, __uint_as_float(li), __uint_as_float(id));
+            s_geo[pos] = q0;
+            s_opa[pos] = make_float4(q1.x, q2.y, q1.y, __uint_as_float(li));
+            s_col[pos] = make_float4(q1.z, q1.w, q2.x, __uint_as_float(id));
         }
         __syncthreads();
 
-        for (int j = 0; j < kept; ++j) {
-            const float4 a = s_q0[j];
-            const float4 b = s_q1[j];
-            const float4 c = s_q2[j];
-            const uint32_t pos_in_list = __float_as_uint(c.z);
+        // Per-warp culling (see render_fwd.cu): each lane tests one staged splat against the
+        // warp's 8x4 pixel block and against the warp's largest n_contrib; the warp visits only
+        // the survivors, in (reverse) list order.
+        for (int base = 0; base < kept; base += 32) {
+        const int jt = base + lane;
+        bool hit = false;
+        if (jt < kept) {
+            const float4 ta = s_geo[jt];
+            const float4 tb = s_opa[jt];
+            hit = __float_as_uint(tb.w) < wmax &&
+                  !tile_rejects(ta.x, ta.y, ta.z, ta.w, tb.x, tb.y, wx0, wy0, wx1, wy1);
+        }
+        unsigned hits = __ballot_sync(0xffffffffu, hit);
+        while (hits) {
+            const int j = base + __ffs(hits) - 1;
+            hits &= hits - 1;
+            const float4 a = s_geo[j];
+            const float4 o = s_opa[j];
+            const uint32_t pos_in_list = __float_as_uint(o.w);
             bool valid = pos_in_list < last_contributor;  // false for pixels outside the image
             const float dx = a.x - pixfx;
             const float dy = a.y - pixfy;
-            const float power = gauss_power(a.z, a.w, b.x, dx, dy);
-            valid = valid && !(power > 0.0f || power < c.y);
+            const float power = gauss_power(a.z, a.w, o.x, dx, dy);
+            valid = valid && !(power > 0.0f || power < o.y);
             if (!__any_sync(0xffffffffu, valid)) continue;
             const float G = expf(power);
-            const float alpha = fminf(0.99f, b.y * G);
+            const float alpha = fminf(0.99f, o.z * G);
             valid = valid && !(alpha < 1.0f / 255.0f);
             if (!__any_sync(0xffffffffu, valid)) continue;
+            const float4 c = s_col[j];
+            // names used by the gradient block below: b = {conic.z, opacity, r, g}, c.x = blue
+            const float4 b = make_float4(o.x, o.z, c.x, c.y);
+            const float cblue = c.z;
 
             float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f, v4 = 0.f, v5 = 0.f, v6 = 0.f, v7 = 0.f,
                   v8 = 0.f;
@@ -142,8 +164,8 @@ render_backward_kernel(int W, int H, const uint2* __restrict__ ranges,
                 lastc1 = b.w;
                 dL_dalpha += (b.w - accum1) * g1;
                 accum2 = last_alpha * lastc2 + one_m_last * accum2;
-                lastc2 = c.x;
-                dL_dalpha += (c.x - accum2) * g2;
+                lastc2 = cblue;
+                dL_dalpha += (cblue - accum2) * g2;
                 dL_dalpha *= T;
                 last_alpha = alpha;
                 dL_dalpha += (-T_final / one_m_alpha) * bg_dot_dpixel;
@@ -192,6 +214,7 @@ render_backward_kernel(int W, int H, const uint2* __restrict__ ranges,
             } else if (lane == 1) {
                 atomicAdd(row + 8, v8);
             }
+        }
         }
     }
 }

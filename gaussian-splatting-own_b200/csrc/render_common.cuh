@@ -56,7 +56,7 @@ __device__ __forceinline__ bool tile_rejects(float mx, float my, float cx, float
     if (!in_x) {
         // vertical edge facing the centre: dx = e fixed, minimise over dy
         const float e = (dx_lo > 0.0f) ? dx_lo : dx_hi;
-        float dy = -cy * e / cz;
+        float dy = __fdividef(-cy * e, cz);  // minimiser position: a 2-ulp error moves q by O(ulp^2)
         dy = fminf(fmaxf(dy, dy_lo), dy_hi);
         const float a = 0.5f * cx * e * e, b = 0.5f * cz * dy * dy, c = cy * e * dy;
         const float q = a + b + c;
@@ -64,7 +64,7 @@ __device__ __forceinline__ bool tile_rejects(float mx, float my, float cx, float
     }
     if (!in_y) {
         const float e = (dy_lo > 0.0f) ? dy_lo : dy_hi;
-        float dx = -cy * e / cx;
+        float dx = __fdividef(-cy * e, cx);
         dx = fminf(fmaxf(dx, dx_lo), dx_hi);
         const float a = 0.5f * cz * e * e, b = 0.5f * cx * dx * dx, c = cy * e * dx;
         const float q = a + b + c;

@@ -10,9 +10,11 @@
 //  * the fetching thread runs an exact-conservative splat/tile rejection test (render_common.cuh)
 //    and the batch is order-preservingly compacted in shared memory (ballot + prefix), so the
 //    256 pixel threads only iterate over splats that can reach alpha >= 1/255 somewhere in the tile;
+//  * a second, per-warp culling level: warps own 8x4 pixel blocks; 32 staged splats at a time are
+//    tested (one per lane) against the warp's block and only the survivors are visited, so a pair
+//    that cannot contribute costs ~2 issued instructions instead of ~18;
 //  * per pair, a single compare against the precomputed log-threshold skips the expf for pairs
-//    whose alpha is provably < 1/255;
-//  * warps own 8x4 pixel blocks.
+//    whose alpha is provably < 1/255.
 #include "render_common.cuh"
 
 namespace bgr {
@@ -32,11 +34,15 @@ render_forward_kernel(int W, int H, const uint2* __restrict__ ranges,
                       uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
                       unsigned long long* __restrict__ stats)
 {
-    unsigned long long st_kept = 0, st_exam = 0, st_exp = 0, st_blend = 0;
-    __shared__ float4 s_q0[RENDER_THREADS];   // x, y, conic.x, conic.y
-    __shared__ float4 s_q1[RENDER_THREADS];   // conic.z, opacity, r, g
-    __shared__ float4 s_q2[RENDER_THREADS];   // b, thr, (list position + 1) as bits, unused
+    // Staged splats of the current round, split by when a field is needed:
+    //   s_geo : x, y, conic.x, conic.y            (culling test + every pair)
+    //   s_opa : conic.z, thr, opacity, list pos+1 (culling test + every pair)
+    //   s_col : r, g, b                            (only pairs that blend)
+    __shared__ float4 s_geo[RENDER_THREADS];
+    __shared__ float4 s_opa[RENDER_THREADS];
+    __shared__ float4 s_col[RENDER_THREADS];
     __shared__ uint32_t s_warp_count[RENDER_WARPS];
+    unsigned long long st_kept = 0, st_exam = 0, st_exp = 0, st_blend = 0;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t tiles_x = (W + TILE_X - 1) / TILE_X;
@@ -50,6 +56,11 @@ render_forward_kernel(int W, int H, const uint2* __restrict__ ranges,
     const float rx0 = (float)tile_px, ry0 = (float)tile_py;
     const float rx1 = (float)min(tile_px + TILE_X - 1, (uint32_t)W - 1);
     const float ry1 = (float)min(tile_py + TILE_Y - 1, (uint32_t)H - 1);
+    // ... and of this warp's 8x4 pixel block
+    const uint32_t wpx = tile_px + ((warp & 1) << 3), wpy = tile_py + ((warp >> 1) << 2);
+    const float wx0 = (float)wpx, wy0 = (float)wpy;
+    const float wx1 = (float)min(wpx + 7, (uint32_t)W - 1);
+    const float wy1 = (float)min(wpy + 3, (uint32_t)H - 1);
 
     const uint2 range = ranges[blockIdx.y * tiles_x + blockIdx.x];
     const int total = (int)(range.y - range.x);
@@ -88,36 +99,52 @@ render_forward_kernel(int W, int H, const uint2* __restrict__ ranges,
         }
         if (keep) {
             const int pos = before + __popc(kmask & ((1u << lane) - 1u));
-            s_q0[pos] = q0;
-            s_q1[pos] = q1;
-            s_q2[pos] = make_float4(q2.x, q2.y, __uint_as_float((uint32_t)progress + 1u), 0.f);
+            s_geo[pos] = q0;
+            s_opa[pos] = make_float4(q1.x, q2.y, q1.y, __uint_as_float((uint32_t)progress + 1u));
+            s_col[pos] = make_float4(q1.z, q1.w, q2.x, 0.f);
         }
         __syncthreads();
         if (kStats && tid == 0) st_kept += (unsigned long long)kept;
 
-        for (int j = 0; !done && j < kept; ++j) {
-            const float4 a = s_q0[j];
-            const float4 b = s_q1[j];
-            const float4 c = s_q2[j];
-            const float dx = a.x - pixfx;
-            const float dy = a.y - pixfy;
-            const float power = gauss_power(a.z, a.w, b.x, dx, dy);
-            if (kStats) ++st_exam;
-            if (power > 0.0f || power < c.y) continue;
-            const float alpha = fminf(0.99f, b.y * expf(power));
-            if (kStats) ++st_exp;
-            if (alpha < 1.0f / 255.0f) continue;
-            const float test_T = T * (1 - alpha);
-            if (test_T < 0.0001f) {
-                done = true;
-                continue;
+        // Per-warp culling: 32 staged splats at a time, each lane tests one of them against the
+        // warp's 8x4 pixel block; the warp then visits only the survivors, in list order.
+        for (int base = 0; base < kept; base += 32) {
+            if (__all_sync(0xffffffffu, done)) break;
+            const int jt = base + lane;
+            bool hit = false;
+            if (jt < kept) {
+                const float4 a = s_geo[jt];
+                const float4 b = s_opa[jt];
+                hit = !tile_rejects(a.x, a.y, a.z, a.w, b.x, b.y, wx0, wy0, wx1, wy1);
             }
-            C0 = __fmaf_rn(__fmul_rn(b.z, alpha), T, C0);
-            C1 = __fmaf_rn(__fmul_rn(b.w, alpha), T, C1);
-            C2 = __fmaf_rn(__fmul_rn(c.x, alpha), T, C2);
-            T = test_T;
-            last_contributor = __float_as_uint(c.z);
-            if (kStats) ++st_blend;
+            unsigned hits = __ballot_sync(0xffffffffu, hit);
+            while (hits) {
+                const int j = base + __ffs(hits) - 1;
+                hits &= hits - 1;
+                if (done) continue;
+                const float4 a = s_geo[j];
+                const float4 b = s_opa[j];
+                const float dx = a.x - pixfx;
+                const float dy = a.y - pixfy;
+                const float power = gauss_power(a.z, a.w, b.x, dx, dy);
+                if (kStats) ++st_exam;
+                if (power > 0.0f || power < b.y) continue;
+                const float alpha = fminf(0.99f, b.z * expf(power));
+                if (kStats) ++st_exp;
+                if (alpha < 1.0f / 255.0f) continue;
+                const float test_T = T * (1 - alpha);
+                if (test_T < 0.0001f) {
+                    done = true;
+                    continue;
+                }
+                const float4 c = s_col[j];
+                C0 = __fmaf_rn(__fmul_rn(c.x, alpha), T, C0);
+                C1 = __fmaf_rn(__fmul_rn(c.y, alpha), T, C1);
+                C2 = __fmaf_rn(__fmul_rn(c.z, alpha), T, C2);
+                T = test_T;
+                last_contributor = __float_as_uint(b.w);
+                if (kStats) ++st_blend;
+            }
         }
     }
 

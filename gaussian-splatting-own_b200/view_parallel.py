@@ -1,0 +1,134 @@
+"""View-batch data parallelism around the rasterizer.
+
+The reference is single-GPU and renders one view per step (train.py:76-86). The path shards
+naturally over views: every rank holds the full, replicated Gaussian set, renders a different
+camera, and the per-Gaussian gradients of the trainer's leaves are summed across ranks before the
+optimizer — ONE exchange step, no other data-path collective.
+
+What is specific to this implementation:
+
+* the backward kernels write the five leaf gradients (means3D 3, sh 3M, opacity 1, scales 3,
+  rotations 4 floats per Gaussian = 59 at M = 16) into one contiguous arena
+  (diff_gaussian_rasterization/_C.py: rasterize_gaussians_backward), so the all-reduce runs IN
+  PLACE on the memory the kernels produced — no pack / unpack copies, one NCCL call for 708 MB at
+  3M Gaussians instead of five;
+* the collective is issued on the same stream right behind the backward, `async_op` optional, so
+  a trainer can overlap it with its loss bookkeeping.
+
+`torch.distributed` (NCCL on GPUs, gloo in the CPU tests) is plumbing only.
+"""
+from __future__ import annotations
+
+from typing import Callable, NamedTuple, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+LEAF_ORDER = ("means3D", "shs", "opacities", "scales", "rotations")
+# index of each leaf's gradient in the 8-tuple returned by rasterize_gaussians_backward
+_GRAD_INDEX = {"means3D": 3, "shs": 5, "opacities": 2, "scales": 6, "rotations": 7}
+
+
+def view_for_rank(step: int, world: int, rank: int, num_views: int) -> int:
+    """Camera index rendered by `rank` at `step`: views are dealt round-robin, `world` per step,
+    wrapping around the view list (the DP analogue of train.py:76-79's one random view per step)."""
+    if num_views <= 0:
+        raise ValueError("no views")
+    return (step * world + rank) % num_views
+
+
+def flat_leaf_gradients(grads: Sequence[torch.Tensor]) -> tuple[torch.Tensor, bool]:
+    """Returns (flat, aliased). If the five leaf gradients already sit back to back in one
+    allocation (the layout libbgr's backward produces) `flat` is a zero-copy view over them and
+    `aliased` is True; otherwise they are packed into a new buffer (reference backend, stubs)."""
+    parts = [grads[_GRAD_INDEX[k]] for k in LEAF_ORDER]
+    base = parts[0]
+    contiguous = all(p.is_contiguous() for p in parts)
+    if contiguous and base._base is not None:
+        ptr = base.data_ptr()
+        ok = True
+        for p in parts:
+            ok = ok and p.data_ptr() == ptr and p._base is base._base
+            ptr += p.numel() * p.element_size()
+        if ok:
+            root = base._base
+            start = (base.data_ptr() - root.data_ptr()) // root.element_size()
+            n = sum(p.numel() for p in parts)
+            return root.view(-1)[start:start + n], True
+    return torch.cat([p.reshape(-1) for p in parts]), False
+
+
+def scatter_flat(flat: torch.Tensor, grads: Sequence[torch.Tensor]) -> None:
+    """Inverse of the packing branch of flat_leaf_gradients."""
+    o = 0
+    for k in LEAF_ORDER:
+        g = grads[_GRAD_INDEX[k]]
+        g.copy_(flat[o:o + g.numel()].view_as(g))
+        o += g.numel()
+
+
+class StepResult(NamedTuple):
+    color: torch.Tensor
+    radii: torch.Tensor
+    num_rendered: int
+    grads: tuple           # the backend's 8-tuple; leaf entries hold the SUM over ranks
+    work: Optional[object]  # async handle of the all-reduce (None when finished or world == 1)
+
+
+class ViewParallelRasterizer:
+    """forward + backward of one view per rank and the gradient exchange.
+
+    backend: module/object with the reference's `_C` call signatures (defaults to libbgr).
+    loss_grad: callable(color) -> dL/dcolor (the trainer's loss backward; a stub in the bench).
+    """
+
+    def __init__(self, backend=None, group: Optional[dist.ProcessGroup] = None, average: bool = False):
+        if backend is None:
+            from diff_gaussian_rasterization import _C as backend  # noqa: N811
+        self.backend = backend
+        self.group = group
+        self.average = average
+
+    @property
+    def world(self) -> int:
+        return dist.get_world_size(self.group) if dist.is_available() and dist.is_initialized() else 1
+
+    def step(self, scene: dict, cam, bg: torch.Tensor, loss_grad: Callable[[torch.Tensor], torch.Tensor],
+             sh_degree: int = 3, scale_modifier: float = 1.0, async_op: bool = False) -> StepResult:
+        e = torch.Tensor([])
+        dev = scene["means3D"].device
+        view, proj, campos = (cam.viewmatrix.to(dev), cam.projmatrix.to(dev), cam.campos.to(dev))
+        fwd = self.backend.rasterize_gaussians(
+            bg, scene["means3D"], e, scene["opacities"], scene["scales"], scene["rotations"],
+            scale_modifier, e, view, proj, cam.tanfovx, cam.tanfovy, cam.image_height,
+            cam.image_width, scene["shs"], sh_degree, campos, False, False)
+        R, color, radii, geom, binning, img = fwd
+        dL_dpix = loss_grad(color)
+        if self.average and self.world > 1:
+            dL_dpix = dL_dpix / self.world     # fold the 1/G of a mean into the upstream gradient
+        grads = self.backend.rasterize_gaussians_backward(
+            bg, scene["means3D"], radii, e, scene["scales"], scene["rotations"], scale_modifier, e,
+            view, proj, cam.tanfovx, cam.tanfovy, dL_dpix, scene["shs"], sh_degree, campos, geom, R,
+            binning, img, False)
+        work = None
+        if self.world > 1:
+            flat, aliased = flat_leaf_gradients(grads)
+            work = dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=async_op)
+            if not aliased:
+                if work is not None:
+                    work.wait()
+                    work = None
+                scatter_flat(flat, grads)
+        return StepResult(color, radii, int(R), tuple(grads), work)
+
+
+def visibility_statistics(radii: torch.Tensor, dL_dmeans2D: torch.Tensor,
+                          group: Optional[dist.ProcessGroup] = None) -> tuple[torch.Tensor, torch.Tensor]:
+    """Densification statistics of the view batch (scene/gaussian_model.py:405-407 per view):
+    sum over ranks of ||dL/dmean2D[:, :2]|| for visible Gaussians and of the visibility count."""
+    vis = radii > 0
+    norm = torch.where(vis, dL_dmeans2D[:, :2].norm(dim=-1), torch.zeros((), device=radii.device))
+    stats = torch.stack([norm, vis.to(norm.dtype)])
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(stats, group=group)
+    return stats[0], stats[1]
