@@ -54,6 +54,8 @@ def parse_args():
     ap.add_argument("--res", choices=("800x800", "1080p", "4k"), default="1080p")
     ap.add_argument("--skip-cpu-baseline", action="store_true")
     ap.add_argument("--skip-e2e", action="store_true")
+    ap.add_argument("--exchange", choices=("nvls", "nccl"), default="nvls",
+                    help="N > 1, ours: in-switch multimem kernel of libbgr (default) or ncclAllReduce")
     return ap.parse_args()
 
 
@@ -156,16 +158,22 @@ class Workload:
                 binning, img, False)
 
 
-def make_native_step(backend, wl, world, impl):
+def make_native_step(backend, wl, world, impl, exchange="nccl"):
     """forward + backward through the backend's `_C`-signature calls; N > 1 adds the all-reduce."""
     import torch.distributed as dist
     import view_parallel as vp
+    nvls = None
+    if world > 1 and impl == "ours" and exchange == "nvls":
+        nvls = vp.NvlsExchange(wl.P, 16, wl.device)
+    make_native_step.nvls = nvls
 
     def step():
         out = backend.rasterize_gaussians(*wl.fwd_args())
         grads = backend.rasterize_gaussians_backward(*wl.bwd_args(out))
         if world > 1:
-            if impl == "ours":
+            if nvls is not None:
+                nvls.all_reduce()                                     # in-switch sum, own kernel
+            elif impl == "ours":
                 flat, aliased = vp.flat_leaf_gradients(grads)         # zero-copy view of the arena
                 assert aliased
                 dist.all_reduce(flat)                                 # in place, one collective
@@ -218,8 +226,13 @@ def make_e2e_step(backend, wl, world, impl):
         loss = (color * w_dev).sum()
         loss.backward()
         if world > 1:
-            for t in leaves.values():
-                dist.all_reduce(t.grad)
+            nvls = getattr(make_native_step, "nvls", None)
+            g0 = leaves["means3D"].grad
+            if nvls is not None and g0.data_ptr() == nvls.buf.data_ptr() + 4 * 12 * wl.P:
+                nvls.all_reduce()      # autograd handed out views of the symmetric arena: in place
+            else:
+                for t in leaves.values():
+                    dist.all_reduce(t.grad)
         loss_host.copy_(loss.detach(), non_blocking=True)
         torch.cuda.current_stream().synchronize()
         return float(loss_host)
@@ -371,7 +384,7 @@ def main():
         dist.init_process_group("nccl", device_id=device)
 
     wl = Workload(args, rank, device)
-    native = make_native_step(backend, wl, world, args.impl)
+    native = make_native_step(backend, wl, world, args.impl, args.exchange)
 
     launches0 = backend.launch_count() if args.impl == "ours" else 0
     native()  # first call: lazy init (pinned control block, func attributes)
@@ -403,7 +416,7 @@ def main():
         "config": {"workload": f"{wl.P} Gaussians SH3 @ {wl.W}x{wl.H}, one camera per GPU "
                                f"(BASELINE.json configs[2]; seeded scene of SURVEY.md 8d)",
                    "gaussians": wl.P, "width": wl.W, "height": wl.H, "sh_degree": 3,
-                   "parallelism": f"view-batch dp{world}" + (", all-reduce of 59 floats/Gaussian" if world > 1 else ""),
+                   "parallelism": f"view-batch dp{world}" + (f", all-reduce of 59 floats/Gaussian ({args.exchange if args.impl == 'ours' else 'nccl'})" if world > 1 else ""),
                    "l2": "no flush: per-step inputs (708 MB at 3M) exceed the 126 MB L2"},
         "e2e": e2e, "clocks": clocks,
     }

@@ -412,6 +412,16 @@ BGR_API int bgr_render_stats(int P, int R, int width, int height, const void* ge
     return rc;
 }
 
+BGR_API int bgr_nvls_allreduce_f32(void* multicast_ptr, size_t offset_floats, size_t count_floats,
+                                   int rank, int world, int max_blocks, void* stream_v)
+{
+    cudaStream_t s = static_cast<cudaStream_t>(stream_v);
+    if (bgr::launch_nvls_allreduce(multicast_ptr, offset_floats, count_floats, rank, world,
+                                   max_blocks, s) != 0)
+        return fail(BGR_ERR_INVALID_ARG, "bad NVLS all-reduce arguments (NULL multicast pointer, rank, or unaligned offset)");
+    return stage_check(false, s, "nvls all-reduce");
+}
+
 BGR_API size_t bgr_sort_temp_bytes(size_t n) { return bgr::sort_temp_layout(n).total; }
 
 BGR_API int bgr_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, size_t n,

@@ -188,6 +188,9 @@ void launch_render_backward(int W, int H, const uint2* ranges, const uint32_t* p
                             const float* final_T, const uint32_t* n_contrib, const float* dL_dpix,
                             float* acc, cudaStream_t s);
 
+int launch_nvls_allreduce(void* multicast_ptr, size_t offset, size_t count, int rank, int world,
+                          int max_blocks, cudaStream_t s);
+
 struct PreprocessBackwardParams {
     int P, D, M, W, H;
     const float* means3D; const int* radii; const float* shs; const float* scales;

@@ -90,6 +90,9 @@ def lib() -> C.CDLL:
     L.bgr_scan_temp_bytes.argtypes = [C.c_size_t]
     L.bgr_inclusive_scan_u32.restype = C.c_int
     L.bgr_inclusive_scan_u32.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
+    L.bgr_nvls_allreduce_f32.restype = C.c_int
+    L.bgr_nvls_allreduce_f32.argtypes = [C.c_void_p, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int,
+                                         C.c_void_p]
     L.bgr_launch_count.restype = C.c_ulonglong
     L.bgr_launch_count.argtypes = []
     L.bgr_stage_timing.restype = None
@@ -216,7 +219,12 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
         # and is contiguous so that a data-parallel caller can all-reduce it in place with one
         # collective (leaf_grad_arena below) — the kernels write straight into the send buffer.
         widths = (3, 3, 6, 3, 3 * M, 1, 3, 4)
-        arena = torch.empty((P * sum(widths),), dtype=torch.float32, device=dev)
+        n_arena = P * sum(widths)
+        arena = _grad_arena_provider(n_arena, dev) if _grad_arena_provider else None
+        if arena is None:
+            arena = torch.empty((n_arena,), dtype=torch.float32, device=dev)
+        elif arena.numel() != n_arena or arena.dtype != torch.float32 or not arena.is_contiguous():
+            raise RuntimeError("gradient arena provider returned a tensor of the wrong size/dtype")
         parts, o = [], 0
         for w in widths:
             parts.append(arena[o:o + P * w])
@@ -268,6 +276,26 @@ def mark_visible(means3D, viewmatrix, projmatrix):
             _check(lib().bgr_mark_visible(P, m.data_ptr(), v.data_ptr(), pj.data_ptr(),
                                           present.data_ptr(), _stream(dev)))
     return present
+
+
+_grad_arena_provider = None
+
+
+def set_grad_arena_provider(fn) -> None:
+    """fn(numel, device) -> flat f32 tensor (or None) that rasterize_gaussians_backward uses for its
+    outputs instead of a fresh allocation. The view-parallel path points it at a buffer in
+    symmetric (peer-mapped, multicast-bound) memory so that the backward kernels write straight
+    into the memory the NVLS all-reduce operates on. The previous call's gradients are
+    overwritten by the next call."""
+    global _grad_arena_provider
+    _grad_arena_provider = fn
+
+
+def nvls_allreduce(multicast_ptr: int, offset_floats: int, count_floats: int, rank: int, world: int,
+                   device, max_blocks: int = 296) -> None:
+    with torch.cuda.device(device):
+        _check(lib().bgr_nvls_allreduce_f32(C.c_void_p(multicast_ptr), offset_floats, count_floats,
+                                            rank, world, max_blocks, _stream(device)))
 
 
 def leaf_grad_arena(grads) -> torch.Tensor:

@@ -67,6 +67,46 @@ def scatter_flat(flat: torch.Tensor, grads: Sequence[torch.Tensor]) -> None:
         o += g.numel()
 
 
+class NvlsExchange:
+    """The gradient arena in symmetric memory + the in-switch sum over it (libbgr's
+    bgr_nvls_allreduce_f32). One instance per (P, M); construction is collective (rendezvous)."""
+
+    NON_LEAF_FLOATS = 12   # means2D 3 + colors 3 + cov3D 6 precede the leaf block in the arena
+
+    def __init__(self, P: int, M: int, device, group: Optional[dist.ProcessGroup] = None,
+                 max_blocks: int = 296):
+        import torch.distributed._symmetric_memory as symm_mem
+        from diff_gaussian_rasterization import _C
+        self._C = _C
+        self.P, self.M, self.device = P, M, torch.device(device)
+        self.leaf_floats = 3 + 3 * M + 1 + 3 + 4
+        self.numel = P * (self.NON_LEAF_FLOATS + self.leaf_floats)
+        self.max_blocks = max_blocks
+        grp = group if group is not None else dist.group.WORLD
+        self.buf = symm_mem.empty(self.numel, dtype=torch.float32, device=self.device)
+        self.hdl = symm_mem.rendezvous(self.buf, grp)
+        if not self.hdl.has_multicast_support(self.device.type, self.device.index or 0) \
+                or not self.hdl.multicast_ptr:
+            raise RuntimeError("NVLink multicast (NVLS) is not available for this group")
+        self.rank, self.world = self.hdl.rank, self.hdl.world_size
+        _C.set_grad_arena_provider(self._provide)
+
+    def _provide(self, numel, dev):
+        return self.buf if (numel == self.numel and torch.device(dev) == self.buf.device) else None
+
+    def all_reduce(self, offset_floats: Optional[int] = None, count_floats: Optional[int] = None):
+        """Sum of the leaf block (default) across ranks, in place, on the current stream."""
+        off = self.P * self.NON_LEAF_FLOATS if offset_floats is None else offset_floats
+        cnt = self.P * self.leaf_floats if count_floats is None else count_floats
+        self.hdl.barrier(channel=0)        # every rank's backward has written its arena
+        self._C.nvls_allreduce(self.hdl.multicast_ptr, off, cnt, self.rank, self.world, self.device,
+                               self.max_blocks)
+        self.hdl.barrier(channel=0)        # every share has been broadcast to every rank
+
+    def close(self):
+        self._C.set_grad_arena_provider(None)
+
+
 class StepResult(NamedTuple):
     color: torch.Tensor
     radii: torch.Tensor
@@ -82,12 +122,17 @@ class ViewParallelRasterizer:
     loss_grad: callable(color) -> dL/dcolor (the trainer's loss backward; a stub in the bench).
     """
 
-    def __init__(self, backend=None, group: Optional[dist.ProcessGroup] = None, average: bool = False):
+    def __init__(self, backend=None, group: Optional[dist.ProcessGroup] = None, average: bool = False,
+                 exchange: str = "nccl"):
         if backend is None:
             from diff_gaussian_rasterization import _C as backend  # noqa: N811
         self.backend = backend
         self.group = group
         self.average = average
+        if exchange not in ("nccl", "nvls"):
+            raise ValueError("exchange must be 'nccl' or 'nvls'")
+        self.exchange = exchange
+        self._nvls: Optional[NvlsExchange] = None
 
     @property
     def world(self) -> int:
@@ -103,6 +148,8 @@ class ViewParallelRasterizer:
             scale_modifier, e, view, proj, cam.tanfovx, cam.tanfovy, cam.image_height,
             cam.image_width, scene["shs"], sh_degree, campos, False, False)
         R, color, radii, geom, binning, img = fwd
+        if self.exchange == "nvls" and self.world > 1 and self._nvls is None:
+            self._nvls = NvlsExchange(scene["means3D"].size(0), scene["shs"].size(1), dev, self.group)
         dL_dpix = loss_grad(color)
         if self.average and self.world > 1:
             dL_dpix = dL_dpix / self.world     # fold the 1/G of a mean into the upstream gradient
@@ -111,7 +158,9 @@ class ViewParallelRasterizer:
             view, proj, cam.tanfovx, cam.tanfovy, dL_dpix, scene["shs"], sh_degree, campos, geom, R,
             binning, img, False)
         work = None
-        if self.world > 1:
+        if self.world > 1 and self._nvls is not None:
+            self._nvls.all_reduce()
+        elif self.world > 1:
             flat, aliased = flat_leaf_gradients(grads)
             work = dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=async_op)
             if not aliased:

@@ -150,6 +150,15 @@ BGR_API int bgr_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a,
 BGR_API size_t bgr_scan_temp_bytes(size_t n);
 BGR_API int bgr_inclusive_scan_u32(const uint32_t* in, uint32_t* out, size_t n, void* temp, void* stream);
 
+/* ---- view-parallel exchange (new; the reference has no multi-GPU path) ---------- */
+/* In-switch (NVLink multicast / NVLS) sum of floats [offset, offset+count) of a buffer that is
+ * symmetrically mapped on `world` GPUs and bound to the multicast address `multicast_ptr`. Rank
+ * `rank` reduces and re-broadcasts its 1/world share with multimem.ld_reduce / multimem.st. The
+ * caller orders it against the other ranks with a cross-GPU barrier before and after (the kernel
+ * never waits on a peer). offset_floats must be a multiple of 4. */
+BGR_API int bgr_nvls_allreduce_f32(void* multicast_ptr, size_t offset_floats, size_t count_floats,
+                                   int rank, int world, int max_blocks, void* stream);
+
 /* ---- diagnostics (bench.py / tests; nothing here is on the product path) --------------------- */
 /* Total number of CUDA kernels this library has launched in this process. */
 BGR_API unsigned long long bgr_launch_count(void);
