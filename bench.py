@@ -54,7 +54,7 @@ def parse_args():
     ap.add_argument("--res", choices=("800x800", "1080p", "4k"), default="1080p")
     ap.add_argument("--skip-cpu-baseline", action="store_true")
     ap.add_argument("--skip-e2e", action="store_true")
-    ap.add_argument("--exchange", choices=("nvls", "nccl"), default="nvls",
+    ap.add_argument("--exchange", choices=("nvls", "nvls-dense", "nccl"), default="nvls",
                     help="N > 1, ours: in-switch multimem kernel of libbgr (default) or ncclAllReduce")
     return ap.parse_args()
 
@@ -163,12 +163,14 @@ def make_native_step(backend, wl, world, impl, exchange="nccl"):
     import torch.distributed as dist
     import view_parallel as vp
     nvls = None
-    if world > 1 and impl == "ours" and exchange == "nvls":
-        nvls = vp.NvlsExchange(wl.P, 16, wl.device)
+    if world > 1 and impl == "ours" and exchange in ("nvls", "nvls-dense"):
+        nvls = vp.NvlsExchange(wl.P, 16, wl.device, sparse=(exchange == "nvls"))
     make_native_step.nvls = nvls
 
     def step():
         out = backend.rasterize_gaussians(*wl.fwd_args())
+        if nvls is not None:
+            nvls.begin(out[2])                                        # visibility OR over ranks
         grads = backend.rasterize_gaussians_backward(*wl.bwd_args(out))
         if world > 1:
             if nvls is not None:
@@ -219,14 +221,16 @@ def make_e2e_step(backend, wl, world, impl):
             projmatrix=cam_dev[16:32].view(4, 4), sh_degree=3, campos=cam_dev[32:35],
             prefiltered=False, debug=False)
         means2D = torch.zeros_like(leaves["means3D"], requires_grad=True)
-        color, _radii = Rasterizer(settings)(
+        color, radii_ = Rasterizer(settings)(
             means3D=leaves["means3D"], means2D=means2D, shs=leaves["shs"], colors_precomp=None,
             opacities=leaves["opacities"], scales=leaves["scales"], rotations=leaves["rotations"],
             cov3D_precomp=None)
+        nvls = getattr(make_native_step, "nvls", None) if world > 1 else None
+        if nvls is not None:
+            nvls.begin(radii_)
         loss = (color * w_dev).sum()
         loss.backward()
         if world > 1:
-            nvls = getattr(make_native_step, "nvls", None)
             g0 = leaves["means3D"].grad
             if nvls is not None and g0.data_ptr() == nvls.buf.data_ptr() + 4 * 12 * wl.P:
                 nvls.all_reduce()      # autograd handed out views of the symmetric arena: in place

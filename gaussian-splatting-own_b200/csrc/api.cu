@@ -422,6 +422,33 @@ BGR_API int bgr_nvls_allreduce_f32(void* multicast_ptr, size_t offset_floats, si
     return stage_check(false, s, "nvls all-reduce");
 }
 
+BGR_API int bgr_nvls_visibility_or(const int* radii, int P, uint32_t* local_words,
+                                   void* multicast_words, int rank, int world, int phase, void* stream_v)
+{
+    cudaStream_t s = static_cast<cudaStream_t>(stream_v);
+    if (P < 0 || (phase != 0 && phase != 1)) return fail(BGR_ERR_INVALID_ARG, "bad argument");
+    if (phase == 0) {
+        if (radii == nullptr || local_words == nullptr) return fail(BGR_ERR_INVALID_ARG, "NULL pointer");
+        bgr::launch_pack_visibility(radii, P, local_words, s);
+    } else if (bgr::launch_nvls_or(multicast_words, ((size_t)P + 31) / 32, rank, world, s) != 0) {
+        return fail(BGR_ERR_INVALID_ARG, "bad NVLS OR arguments");
+    }
+    return stage_check(false, s, "nvls visibility");
+}
+
+BGR_API int bgr_nvls_allreduce_rows_f32(void* multicast_a, int floats_a, void* multicast_b, int floats_b,
+                                        const uint32_t* vis_words, size_t rows, int rank, int world,
+                                        int max_blocks, void* stream_v)
+{
+    cudaStream_t s = static_cast<cudaStream_t>(stream_v);
+    if ((floats_a & 3) != 0 || (floats_b & 3) != 0)
+        return fail(BGR_ERR_INVALID_ARG, "row widths must be multiples of 4 floats");
+    if (bgr::launch_nvls_sparse_rows(multicast_a, floats_a / 4, multicast_b, floats_b / 4, vis_words, rows,
+                                     rank, world, max_blocks, s) != 0)
+        return fail(BGR_ERR_INVALID_ARG, "bad sparse NVLS arguments (NULL/unaligned pointer, rank, or row wider than 64 floats)");
+    return stage_check(false, s, "nvls sparse rows");
+}
+
 BGR_API size_t bgr_sort_temp_bytes(size_t n) { return bgr::sort_temp_layout(n).total; }
 
 BGR_API int bgr_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, size_t n,

@@ -191,6 +191,11 @@ void launch_render_backward(int W, int H, const uint2* ranges, const uint32_t* p
 int launch_nvls_allreduce(void* multicast_ptr, size_t offset, size_t count, int rank, int world,
                           int max_blocks, cudaStream_t s);
 
+void launch_pack_visibility(const int* radii, int P, uint32_t* words, cudaStream_t s);
+int launch_nvls_or(void* multicast_words, size_t nwords, int rank, int world, cudaStream_t s);
+int launch_nvls_sparse_rows(void* mc_a, int vecs_a, void* mc_b, int vecs_b, const uint32_t* vis_words,
+                            size_t rows, int rank, int world, int max_blocks, cudaStream_t s);
+
 struct PreprocessBackwardParams {
     int P, D, M, W, H;
     const float* means3D; const int* radii; const float* shs; const float* scales;

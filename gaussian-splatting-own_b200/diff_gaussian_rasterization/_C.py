@@ -93,6 +93,12 @@ def lib() -> C.CDLL:
     L.bgr_nvls_allreduce_f32.restype = C.c_int
     L.bgr_nvls_allreduce_f32.argtypes = [C.c_void_p, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int,
                                          C.c_void_p]
+    L.bgr_nvls_visibility_or.restype = C.c_int
+    L.bgr_nvls_visibility_or.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                         C.c_int, C.c_void_p]
+    L.bgr_nvls_allreduce_rows_f32.restype = C.c_int
+    L.bgr_nvls_allreduce_rows_f32.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p,
+                                              C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_void_p]
     L.bgr_launch_count.restype = C.c_ulonglong
     L.bgr_launch_count.argtypes = []
     L.bgr_stage_timing.restype = None
@@ -214,11 +220,13 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     M = int(sh.size(1)) if sh.size(0) != 0 else 0
     with torch.cuda.device(dev):
         # One arena for all outputs: every element is written by the kernels, so no zero fill is
-        # needed. Layout: [means2D | colors | cov3D || means3D | sh | opacity | scales | rotations];
-        # the part after || is what a trainer's leaves receive (59 floats per Gaussian at M=16)
-        # and is contiguous so that a data-parallel caller can all-reduce it in place with one
-        # collective (leaf_grad_arena below) — the kernels write straight into the send buffer.
-        widths = (3, 3, 6, 3, 3 * M, 1, 3, 4)
+        # needed. Layout (floats per Gaussian):
+        #   [means2D 3 | colors 3 | cov3D 6 || means3D 3 | opacity 1 | scales 3 | rotations 4 | sh 3M]
+        # The part after || is what a trainer's leaves receive (59 floats at M = 16) and is
+        # contiguous so that a data-parallel caller can sum it across ranks in place with one
+        # collective — the kernels write straight into the send buffer. The small leaves come
+        # first (dense exchange), rotations + sh last (row-sparse exchange, view_parallel.py).
+        widths = (3, 3, 6, 3, 1, 3, 4, 3 * M)
         n_arena = P * sum(widths)
         arena = _grad_arena_provider(n_arena, dev) if _grad_arena_provider else None
         if arena is None:
@@ -233,10 +241,10 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
         dL_dcolors = parts[1].view(P, 3)
         dL_dcov3D = parts[2].view(P, 6)
         dL_dmeans3D = parts[3].view(P, 3)
-        dL_dsh = parts[4].view(P, M, 3)
-        dL_dopacity = parts[5].view(P, 1)
-        dL_dscales = parts[6].view(P, 3)
-        dL_drotations = parts[7].view(P, 4)
+        dL_dopacity = parts[4].view(P, 1)
+        dL_dscales = parts[5].view(P, 3)
+        dL_drotations = parts[6].view(P, 4)
+        dL_dsh = parts[7].view(P, M, 3)
         if P != 0:
             scratch = torch.empty((L.bgr_backward_scratch_bytes(P),), dtype=torch.uint8, device=dev)
             keep = [_f32c(t, dev) for t in (background, means3D, sh, colors, scales, rotations,
@@ -298,9 +306,26 @@ def nvls_allreduce(multicast_ptr: int, offset_floats: int, count_floats: int, ra
                                             rank, world, max_blocks, _stream(device)))
 
 
+def nvls_visibility(radii, P: int, local_words_ptr: int, multicast_words_ptr: int, rank: int,
+                    world: int, phase: int, device) -> None:
+    with torch.cuda.device(device):
+        _check(lib().bgr_nvls_visibility_or(C.c_void_p(radii.data_ptr() if radii is not None else None),
+                                            int(P), C.c_void_p(local_words_ptr),
+                                            C.c_void_p(multicast_words_ptr), rank, world, phase,
+                                            _stream(device)))
+
+
+def nvls_allreduce_rows(mc_a: int, floats_a: int, mc_b: int, floats_b: int, vis_words_ptr: int,
+                        rows: int, rank: int, world: int, device, max_blocks: int = 296) -> None:
+    with torch.cuda.device(device):
+        _check(lib().bgr_nvls_allreduce_rows_f32(C.c_void_p(mc_a), floats_a, C.c_void_p(mc_b), floats_b,
+                                                 C.c_void_p(vis_words_ptr), rows, rank, world,
+                                                 max_blocks, _stream(device)))
+
+
 def leaf_grad_arena(grads) -> torch.Tensor:
-    """The flat f32 tensor that aliases (dL_dmeans3D, dL_dsh, dL_dopacity, dL_dscales,
-    dL_drotations) of one rasterize_gaussians_backward result, in that order."""
+    """The flat f32 tensor that aliases (dL_dmeans3D, dL_dopacity, dL_dscales, dL_drotations,
+    dL_dsh) of one rasterize_gaussians_backward result, in that (memory) order."""
     dL_dmeans3D, dL_dsh = grads[3], grads[5]
     arena = dL_dmeans3D._base
     P = dL_dmeans3D.size(0)

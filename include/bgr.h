@@ -159,6 +159,17 @@ BGR_API int bgr_inclusive_scan_u32(const uint32_t* in, uint32_t* out, size_t n, 
 BGR_API int bgr_nvls_allreduce_f32(void* multicast_ptr, size_t offset_floats, size_t count_floats,
                                    int rank, int world, int max_blocks, void* stream);
 
+/* Row-sparse variant. A Gaussian that no rank sees has an all-zero gradient row everywhere and need
+ * not cross the fabric. phase 0: packs (radii > 0) into one bit per Gaussian in local_words (part of
+ * the symmetric buffer); [cross-GPU barrier]; phase 1: ORs the words across ranks in the switch. */
+BGR_API int bgr_nvls_visibility_or(const int* radii, int P, uint32_t* local_words,
+                                   void* multicast_words, int rank, int world, int phase, void* stream);
+/* Sums, across ranks, only the rows whose bit is set in vis_words, of two row-major blocks sharing
+ * the row index (a: floats_a per row, b: floats_b per row; multiples of 4, at most 64 in total). */
+BGR_API int bgr_nvls_allreduce_rows_f32(void* multicast_a, int floats_a, void* multicast_b, int floats_b,
+                                        const uint32_t* vis_words, size_t rows, int rank, int world,
+                                        int max_blocks, void* stream);
+
 /* ---- diagnostics (bench.py / tests; nothing here is on the product path) --------------------- */
 /* Total number of CUDA kernels this library has launched in this process. */
 BGR_API unsigned long long bgr_launch_count(void);

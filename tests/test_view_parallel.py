@@ -38,7 +38,7 @@ class StubBackend:
     def rasterize_gaussians_backward(self, bg, means3D, radii, colors, scales, rotations, mod, cov,
                                      view, proj, tx, ty, dL, sh, deg, campos, geom, R, binning, img, debug):
         P, M = means3D.size(0), sh.size(1)
-        widths = (3, 3, 6, 3, 3 * M, 1, 3, 4)
+        widths = (3, 3, 6, 3, 1, 3, 4, 3 * M)
         s = float(dL.sum()) + float(campos[0])
         if self.arena:
             a = torch.empty(P * sum(widths))
@@ -49,7 +49,7 @@ class StubBackend:
             parts = [torch.empty(P * w) for w in widths]
         for k, p in enumerate(parts):
             p.copy_(torch.arange(p.numel(), dtype=torch.float32) * 1e-3 + s * (k + 1))
-        m2, col, cov3, m3, dsh, op, sc, rot = parts
+        m2, col, cov3, m3, op, sc, rot, dsh = parts
         return (m2.view(P, 3), col.view(P, 3), op.view(P, 1), m3.view(P, 3), cov3.view(P, 6),
                 dsh.view(P, M, 3), sc.view(P, 3), rot.view(P, 4))
 
@@ -116,7 +116,7 @@ def test_flat_view_is_zero_copy_for_the_arena_layout():
     flat, aliased = vp.flat_leaf_gradients(g)
     assert aliased and flat.numel() == 7 * 59 and flat.data_ptr() == g[3].data_ptr()
     flat.mul_(2.0)   # in place on the arena == in place on every leaf gradient
-    assert float(g[7][-1, -1]) == pytest.approx(float(flat[-1]))
+    assert float(g[5][-1, -1, -1]) == pytest.approx(float(flat[-1]))
     g2 = StubBackend(False).rasterize_gaussians_backward(
         None, torch.zeros(7, 3), None, None, None, None, 1.0, None, None, None, 0, 0, torch.ones(1),
         torch.zeros(7, 16, 3), 3, torch.zeros(3), None, 0, None, None, False)
@@ -124,15 +124,15 @@ def test_flat_view_is_zero_copy_for_the_arena_layout():
     assert not aliased2 and flat2.numel() == 7 * 59
     flat2.mul_(2.0)
     vp.scatter_flat(flat2, g2)
-    torch.testing.assert_close(torch.cat([g2[i].reshape(-1) for i in (3, 5, 2, 6, 7)]), flat2)
+    torch.testing.assert_close(torch.cat([g2[i].reshape(-1) for i in (3, 2, 6, 7, 5)]), flat2)
 
 
 def test_real_backend_arena_layout_matches():
     """The slicing done by _C.rasterize_gaussians_backward (checked here without a GPU by
     re-deriving its widths) must keep the five leaves adjacent in LEAF_ORDER."""
     src = (ROOT / "gaussian-splatting-own_b200" / "diff_gaussian_rasterization" / "_C.py").read_text()
-    assert "widths = (3, 3, 6, 3, 3 * M, 1, 3, 4)" in src
-    assert vp.LEAF_ORDER == ("means3D", "shs", "opacities", "scales", "rotations")
+    assert "widths = (3, 3, 6, 3, 1, 3, 4, 3 * M)" in src
+    assert vp.LEAF_ORDER == ("means3D", "opacities", "scales", "rotations", "shs")
 
 
 def test_view_dealing_covers_every_view_once_per_epoch():
