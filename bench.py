@@ -54,7 +54,7 @@ def parse_args():
     ap.add_argument("--res", choices=("800x800", "1080p", "4k"), default="1080p")
     ap.add_argument("--skip-cpu-baseline", action="store_true")
     ap.add_argument("--skip-e2e", action="store_true")
-    ap.add_argument("--exchange", choices=("nvls", "nvls-dense", "nccl"), default="nvls",
+    ap.add_argument("--exchange", choices=("nvls", "nvls-rows", "nvls-dense", "nccl"), default="nvls",
                     help="N > 1, ours: in-switch multimem kernel of libbgr (default) or ncclAllReduce")
     return ap.parse_args()
 
@@ -163,8 +163,9 @@ def make_native_step(backend, wl, world, impl, exchange="nccl"):
     import torch.distributed as dist
     import view_parallel as vp
     nvls = None
-    if world > 1 and impl == "ours" and exchange in ("nvls", "nvls-dense"):
-        nvls = vp.NvlsExchange(wl.P, 16, wl.device, sparse=(exchange == "nvls"))
+    if world > 1 and impl == "ours" and exchange.startswith("nvls"):
+        nvls = vp.NvlsExchange(wl.P, 16, wl.device,
+                               mode={"nvls": "factor", "nvls-rows": "rows", "nvls-dense": "dense"}[exchange])
     make_native_step.nvls = nvls
 
     def step():

@@ -360,8 +360,15 @@ BGR_API int bgr_backward(const BgrBackwardArgs* a, void* stream_v)
     pb.dL_dmean2D = a->dL_dmean2D; pb.dL_dcolor = a->dL_dcolor; pb.dL_dopacity = a->dL_dopacity;
     pb.dL_dmean3D = a->dL_dmean3D; pb.dL_dcov3D = a->dL_dcov3D; pb.dL_dsh = a->dL_dsh;
     pb.dL_dscale = a->dL_dscale; pb.dL_drot = a->dL_drot;
-    if (pb.shs != nullptr && pb.dL_dsh == nullptr)
+    pb.factor_mc = a->sh_factor_multicast; pb.campos_mc = a->campos_multicast;
+    if (pb.factor_mc != nullptr) {
+        if (pb.shs == nullptr || pb.campos_mc == nullptr || (a->P & 3) != 0 ||
+            (reinterpret_cast<uintptr_t>(pb.factor_mc) & 15) != 0)
+            return fail(BGR_ERR_INVALID_ARG,
+                        "SH factor multicast needs SHs, a camera slot, P % 4 == 0 and a 16-byte aligned slot");
+    } else if (pb.shs != nullptr && pb.dL_dsh == nullptr) {
         return fail(BGR_ERR_INVALID_ARG, "dL_dsh is NULL although SHs were given");
+    }
     g_timer.begin(ST_PREPROCESS_BWD, s);
     launch_preprocess_backward(pb, s);
     g_timer.end(ST_PREPROCESS_BWD, s);
@@ -420,6 +427,20 @@ BGR_API int bgr_nvls_allreduce_f32(void* multicast_ptr, size_t offset_floats, si
                                    max_blocks, s) != 0)
         return fail(BGR_ERR_INVALID_ARG, "bad NVLS all-reduce arguments (NULL multicast pointer, rank, or unaligned offset)");
     return stage_check(false, s, "nvls all-reduce");
+}
+
+BGR_API int bgr_sh_grad_from_factors(int P, int D, int M, int world, const float* means3D,
+                                     const float* campos_all, const float* factors_all, float* dL_dsh,
+                                     void* stream_v)
+{
+    cudaStream_t s = static_cast<cudaStream_t>(stream_v);
+    if (P < 0 || D < 0 || D > 3 || M < (D + 1) * (D + 1) || world <= 0)
+        return fail(BGR_ERR_INVALID_ARG, "bad sizes");
+    if (P == 0) return BGR_OK;
+    if (means3D == nullptr || campos_all == nullptr || factors_all == nullptr || dL_dsh == nullptr)
+        return fail(BGR_ERR_INVALID_ARG, "required pointer is NULL");
+    bgr::launch_sh_grad_from_factors(P, D, M, world, means3D, campos_all, factors_all, dL_dsh, s);
+    return stage_check(false, s, "sh gradient from factors");
 }
 
 BGR_API int bgr_nvls_visibility_or(const int* radii, int P, uint32_t* local_words,

@@ -206,7 +206,13 @@ struct PreprocessBackwardParams {
     const GaussRec* rec; const float* acc;
     float* dL_dmean2D; float* dL_dcolor; float* dL_dopacity; float* dL_dmean3D; float* dL_dcov3D;
     float* dL_dsh; float* dL_dscale; float* dL_drot;
+    // view-parallel path: multicast address of this rank's factor slot [P][3] and of its camera
+    // position slot [4] (nullptr => write dL_dsh normally)
+    float* factor_mc; float* campos_mc;
 };
 void launch_preprocess_backward(const PreprocessBackwardParams& p, cudaStream_t s);
+void launch_sh_grad_from_factors(int P, int D, int M, int world, const float* means3D,
+                                 const float* campos_all, const float* factors_all, float* dL_dsh,
+                                 cudaStream_t s);
 
 }  // namespace bgr

@@ -20,19 +20,14 @@ __device__ __forceinline__ void store3(float* p, float a, float b, float c)
     p[0] = a; p[1] = b; p[2] = c;
 }
 
-template <bool kVecSH>
-__global__ void __launch_bounds__(PB_THREADS) preprocess_backward_kernel(PreprocessBackwardParams p)
+// Per-Gaussian body. Returns the clamp-masked colour gradient dL/dRGB (zero for culled
+// Gaussians): dL/dsh[k] = basis_k(dir) * dL/dRGB is rank one, which the view-parallel path
+// exploits (kFactor: dL_dsh is NOT written here, the caller multicasts the returned factor).
+template <bool kVecSH, bool kFactor>
+__device__ __forceinline__ V3 preprocess_backward_body(const PreprocessBackwardParams& p, int idx,
+                                                       const float* s_view, const float* s_proj,
+                                                       const float* s_cam)
 {
-    __shared__ float s_view[16], s_proj[16], s_cam[3];
-    if (threadIdx.x < 16) {
-        s_view[threadIdx.x] = p.viewmatrix[threadIdx.x];
-        s_proj[threadIdx.x] = p.projmatrix[threadIdx.x];
-    }
-    if (threadIdx.x < 3) s_cam[threadIdx.x] = p.cam_pos[threadIdx.x];
-    __syncthreads();
-
-    const int idx = blockIdx.x * PB_THREADS + threadIdx.x;
-    if (idx >= p.P) return;
     const size_t i = (size_t)idx;
     const int ncoef = (p.D + 1) * (p.D + 1);
 
@@ -50,7 +45,7 @@ __global__ void __launch_bounds__(PB_THREADS) preprocess_backward_kernel(Preproc
 #pragma unroll
             for (int k = 0; k < 4; ++k) p.dL_drot[4 * i + k] = 0.f;
         }
-        if (p.M > 0) {
+        if (p.M > 0 && !kFactor) {
             if (kVecSH) {
                 float4* dst = reinterpret_cast<float4*>(p.dL_dsh) + i * 12;
 #pragma unroll
@@ -60,8 +55,9 @@ __global__ void __launch_bounds__(PB_THREADS) preprocess_backward_kernel(Preproc
                 for (int k = 0; k < p.M * 3; ++k) dst[k] = 0.f;
             }
         }
-        return;
+        return v3(0.f, 0.f, 0.f);
     }
+    V3 factor = v3(0.f, 0.f, 0.f);
 
     // ---- screen-space gradients accumulated by the backward render ---------------------------
     const float4* arow = reinterpret_cast<const float4*>(p.acc + i * ACC_STRIDE);
@@ -209,6 +205,7 @@ __global__ void __launch_bounds__(PB_THREADS) preprocess_backward_kernel(Preproc
         if (clampbits & 1u) dRGB.x = 0.f;
         if (clampbits & 2u) dRGB.y = 0.f;
         if (clampbits & 4u) dRGB.z = 0.f;
+        factor = dRGB;
 
         const V3 dir_orig = v3(mean.x, mean.y, mean.z) - v3(s_cam[0], s_cam[1], s_cam[2]);
         const V3 dir = dir_orig / length3(dir_orig);
@@ -264,7 +261,9 @@ __global__ void __launch_bounds__(PB_THREADS) preprocess_backward_kernel(Preproc
             for (int k = 0; k < 16; ++k) {
                 const bool on = k < ncoef;
                 const float bk = on ? bas[k] : 0.f;
-                out[3 * k] = bk * dRGB.x; out[3 * k + 1] = bk * dRGB.y; out[3 * k + 2] = bk * dRGB.z;
+                if (!kFactor) {
+                    out[3 * k] = bk * dRGB.x; out[3 * k + 1] = bk * dRGB.y; out[3 * k + 2] = bk * dRGB.z;
+                }
                 if (on && k > 0) {
                     const V3 s = v3(sh[3 * k], sh[3 * k + 1], sh[3 * k + 2]);
                     dRGBdx = dRGBdx + bx[k] * s;
@@ -272,9 +271,11 @@ __global__ void __launch_bounds__(PB_THREADS) preprocess_backward_kernel(Preproc
                     dRGBdz = dRGBdz + bz[k] * s;
                 }
             }
+            if (!kFactor) {
 #pragma unroll
-            for (int k = 0; k < 12; ++k)
-                dst[k] = make_float4(out[4 * k], out[4 * k + 1], out[4 * k + 2], out[4 * k + 3]);
+                for (int k = 0; k < 12; ++k)
+                    dst[k] = make_float4(out[4 * k], out[4 * k + 1], out[4 * k + 2], out[4 * k + 3]);
+            }
         } else {
             const float* src = p.shs + i * p.M * 3;
             float* dst = p.dL_dsh + i * p.M * 3;
@@ -283,7 +284,9 @@ __global__ void __launch_bounds__(PB_THREADS) preprocess_backward_kernel(Preproc
                 if (k < p.M) {
                     const bool on = k < ncoef;
                     const float bk = on ? bas[k] : 0.f;
-                    dst[3 * k] = bk * dRGB.x; dst[3 * k + 1] = bk * dRGB.y; dst[3 * k + 2] = bk * dRGB.z;
+                    if (!kFactor) {
+                        dst[3 * k] = bk * dRGB.x; dst[3 * k + 1] = bk * dRGB.y; dst[3 * k + 2] = bk * dRGB.z;
+                    }
                     if (on && k > 0) {
                         const V3 s = v3(src[3 * k], src[3 * k + 1], src[3 * k + 2]);
                         dRGBdx = dRGBdx + bx[k] * s;
@@ -292,7 +295,8 @@ __global__ void __launch_bounds__(PB_THREADS) preprocess_backward_kernel(Preproc
                     }
                 }
             }
-            for (int k = 16; k < p.M; ++k) store3(dst + 3 * k, 0.f, 0.f, 0.f);
+            if (!kFactor)
+                for (int k = 16; k < p.M; ++k) store3(dst + 3 * k, 0.f, 0.f, 0.f);
         }
 
         const V3 dL_ddir = v3(dot3(dRGBdx, dRGB), dot3(dRGBdy, dRGB), dot3(dRGBdz, dRGB));
@@ -359,22 +363,145 @@ __global__ void __launch_bounds__(PB_THREADS) preprocess_backward_kernel(Preproc
 #pragma unroll
         for (int k = 0; k < 4; ++k) p.dL_drot[4 * i + k] = 0.f;
     }
+    return factor;
+}
+
+__device__ __forceinline__ void mm_st4(float4* p, float4 v)
+{
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x),
+                 "f"(v.y), "f"(v.z), "f"(v.w)
+                 : "memory");
+}
+
+// kFactor (view-parallel path): instead of writing 3M floats of dL/dsh per Gaussian, the block
+// stages its 256 x 3 colour-gradient factors in shared memory and MULTICASTS them (multimem.st:
+// one store, the NVSwitch replicates it) into slot `dp_rank` of a symmetric buffer on every GPU —
+// the all-gather is done by the kernel that produces the data, while it is still computing. Each
+// rank later rebuilds sum_v basis(dir_v) x factor_v locally (sh_grad_from_factors_kernel).
+template <bool kVecSH, bool kFactor>
+__global__ void __launch_bounds__(PB_THREADS) preprocess_backward_kernel(PreprocessBackwardParams p)
+{
+    __shared__ float s_view[16], s_proj[16], s_cam[3];
+    __shared__ __align__(16) float s_factor[kFactor ? 3 * PB_THREADS : 4];
+    if (threadIdx.x < 16) {
+        s_view[threadIdx.x] = p.viewmatrix[threadIdx.x];
+        s_proj[threadIdx.x] = p.projmatrix[threadIdx.x];
+    }
+    if (threadIdx.x < 3) s_cam[threadIdx.x] = p.cam_pos[threadIdx.x];
+    __syncthreads();
+
+    const int idx = blockIdx.x * PB_THREADS + threadIdx.x;
+    V3 f = v3(0.f, 0.f, 0.f);
+    if (idx < p.P) f = preprocess_backward_body<kVecSH, kFactor>(p, idx, s_view, s_proj, s_cam);
+    if (kFactor) {
+        s_factor[3 * threadIdx.x] = f.x;
+        s_factor[3 * threadIdx.x + 1] = f.y;
+        s_factor[3 * threadIdx.x + 2] = f.z;
+        __syncthreads();
+        // 3*256 floats = 192 float4; P % 4 == 0 is required by the host, so the valid part of
+        // the last block is a whole number of float4 too
+        const size_t first = (size_t)blockIdx.x * PB_THREADS * 3;            // float index in the slot
+        const size_t valid = min((size_t)PB_THREADS, (size_t)p.P - (size_t)blockIdx.x * PB_THREADS) * 3;
+        float4* dst = reinterpret_cast<float4*>(p.factor_mc + first);
+        if (threadIdx.x * 4 < valid)
+            mm_st4(dst + threadIdx.x, reinterpret_cast<const float4*>(s_factor)[threadIdx.x]);
+        if (blockIdx.x == 0 && threadIdx.x < 3)
+            asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(p.campos_mc + threadIdx.x),
+                         "f"(s_cam[threadIdx.x])
+                         : "memory");
+    }
+}
+
+// dL/dsh[i][k][c] = sum over views v of basis_k(dir_v(i)) * factor_v[i][c]   (k < (D+1)^2, else 0),
+// summed in rank order, i.e. deterministically and identically on every rank.
+__global__ void __launch_bounds__(256)
+sh_grad_from_factors_kernel(int P, int D, int M, int world, const float* __restrict__ means3D,
+                            const float* __restrict__ campos_all, const float* __restrict__ factors_all,
+                            float* __restrict__ dL_dsh)
+{
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P) return;
+    const size_t i = (size_t)idx;
+    const int ncoef = (D + 1) * (D + 1);
+    float acc[48];
+#pragma unroll
+    for (int k = 0; k < 48; ++k) acc[k] = 0.f;
+    const V3 mean = v3(means3D[3 * i], means3D[3 * i + 1], means3D[3 * i + 2]);
+    for (int v = 0; v < world; ++v) {
+        const float* fsrc = factors_all + ((size_t)v * P + i) * 3;
+        const V3 g = v3(fsrc[0], fsrc[1], fsrc[2]);
+        if (g.x == 0.f && g.y == 0.f && g.z == 0.f) continue;   // not seen (or fully clamped) in view v
+        const V3 cam = v3(campos_all[4 * v], campos_all[4 * v + 1], campos_all[4 * v + 2]);
+        const V3 dir_orig = mean - cam;
+        const V3 dir = dir_orig / length3(dir_orig);
+        const float x = dir.x, y = dir.y, z = dir.z;
+        const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+        float bas[16];
+        bas[0] = kC0;
+        bas[1] = -kC1 * y; bas[2] = kC1 * z; bas[3] = -kC1 * x;
+        bas[4] = kC2_0 * xy; bas[5] = kC2_1 * yz; bas[6] = kC2_2 * (2.f * zz - xx - yy);
+        bas[7] = kC2_3 * xz; bas[8] = kC2_4 * (xx - yy);
+        bas[9] = kC3_0 * y * (3.f * xx - yy); bas[10] = kC3_1 * xy * z;
+        bas[11] = kC3_2 * y * (4.f * zz - xx - yy);
+        bas[12] = kC3_3 * z * (2.f * zz - 3.f * xx - 3.f * yy);
+        bas[13] = kC3_4 * x * (4.f * zz - xx - yy); bas[14] = kC3_5 * z * (xx - yy);
+        bas[15] = kC3_6 * x * (xx - 3.f * yy);
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            if (k < ncoef) {
+                // product rounded first, then added: the same value a plain sum of the per-view
+                // dL/dsh (bas*g rounded by K7) would accumulate
+                acc[3 * k] = __fadd_rn(acc[3 * k], __fmul_rn(bas[k], g.x));
+                acc[3 * k + 1] = __fadd_rn(acc[3 * k + 1], __fmul_rn(bas[k], g.y));
+                acc[3 * k + 2] = __fadd_rn(acc[3 * k + 2], __fmul_rn(bas[k], g.z));
+            }
+        }
+    }
+    if (M == 16 && (reinterpret_cast<uintptr_t>(dL_dsh) & 15) == 0) {
+        float4* dst = reinterpret_cast<float4*>(dL_dsh) + i * 12;
+#pragma unroll
+        for (int k = 0; k < 12; ++k)
+            dst[k] = make_float4(acc[4 * k], acc[4 * k + 1], acc[4 * k + 2], acc[4 * k + 3]);
+    } else {
+        float* dst = dL_dsh + i * M * 3;
+#pragma unroll
+        for (int k = 0; k < 48; ++k)
+            if (k < M * 3) dst[k] = acc[k];
+        for (int k = 48; k < M * 3; ++k) dst[k] = 0.f;
+    }
 }
 
 }  // namespace
+
+void launch_sh_grad_from_factors(int P, int D, int M, int world, const float* means3D,
+                                 const float* campos_all, const float* factors_all, float* dL_dsh,
+                                 cudaStream_t s)
+{
+    if (P <= 0) return;
+    ++g_kernel_launches;
+    sh_grad_from_factors_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, D, M, world, means3D, campos_all,
+                                                               factors_all, dL_dsh);
+}
 
 void launch_preprocess_backward(const PreprocessBackwardParams& p, cudaStream_t s)
 {
     if (p.P <= 0) return;
     const int blocks = (p.P + PB_THREADS - 1) / PB_THREADS;
+    const bool factor = p.factor_mc != nullptr && p.shs != nullptr;
     const bool vec = p.shs != nullptr && p.M == 16 &&
                      (reinterpret_cast<uintptr_t>(p.shs) & 15) == 0 &&
-                     (reinterpret_cast<uintptr_t>(p.dL_dsh) & 15) == 0;
+                     (factor || (reinterpret_cast<uintptr_t>(p.dL_dsh) & 15) == 0);
     ++g_kernel_launches;
-    if (vec)
-        preprocess_backward_kernel<true><<<blocks, PB_THREADS, 0, s>>>(p);
-    else
-        preprocess_backward_kernel<false><<<blocks, PB_THREADS, 0, s>>>(p);
+    if (factor) {
+        if (vec)
+            preprocess_backward_kernel<true, true><<<blocks, PB_THREADS, 0, s>>>(p);
+        else
+            preprocess_backward_kernel<false, true><<<blocks, PB_THREADS, 0, s>>>(p);
+    } else if (vec) {
+        preprocess_backward_kernel<true, false><<<blocks, PB_THREADS, 0, s>>>(p);
+    } else {
+        preprocess_backward_kernel<false, false><<<blocks, PB_THREADS, 0, s>>>(p);
+    }
 }
 
 }  // namespace bgr

@@ -45,6 +45,7 @@ class _BackwardArgs(C.Structure):
         ("dL_dcolor", C.c_void_p), ("dL_dopacity", C.c_void_p), ("dL_dmean3D", C.c_void_p),
         ("dL_dcov3D", C.c_void_p), ("dL_dsh", C.c_void_p), ("dL_dscale", C.c_void_p),
         ("dL_drot", C.c_void_p), ("debug", C.c_int),
+        ("sh_factor_multicast", C.c_void_p), ("campos_multicast", C.c_void_p),
     ]
 
 
@@ -93,6 +94,9 @@ def lib() -> C.CDLL:
     L.bgr_nvls_allreduce_f32.restype = C.c_int
     L.bgr_nvls_allreduce_f32.argtypes = [C.c_void_p, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int,
                                          C.c_void_p]
+    L.bgr_sh_grad_from_factors.restype = C.c_int
+    L.bgr_sh_grad_from_factors.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                           C.c_void_p, C.c_void_p, C.c_void_p]
     L.bgr_nvls_visibility_or.restype = C.c_int
     L.bgr_nvls_visibility_or.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                          C.c_int, C.c_void_p]
@@ -264,6 +268,11 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
                 dL_dcolor=_ptr(dL_dcolors), dL_dopacity=_ptr(dL_dopacity),
                 dL_dmean3D=_ptr(dL_dmeans3D), dL_dcov3D=_ptr(dL_dcov3D), dL_dsh=_ptr(dL_dsh),
                 dL_dscale=_ptr(dL_dscales), dL_drot=_ptr(dL_drotations), debug=int(bool(debug)))
+            if _sh_factor_hook is not None and M > 0:
+                # view-parallel path: multicast dL/dRGB instead of writing dL_dsh (see bgr.h)
+                slots = _sh_factor_hook(P, M, int(degree), means_, dL_dsh)
+                if slots is not None:
+                    a.sh_factor_multicast, a.campos_multicast = slots
             _check(L.bgr_backward(C.byref(a), _stream(dev)))
             # scratch may be reused by the allocator only after the kernels that read it
             scratch.record_stream(torch.cuda.current_stream(dev))
@@ -304,6 +313,26 @@ def nvls_allreduce(multicast_ptr: int, offset_floats: int, count_floats: int, ra
     with torch.cuda.device(device):
         _check(lib().bgr_nvls_allreduce_f32(C.c_void_p(multicast_ptr), offset_floats, count_floats,
                                             rank, world, max_blocks, _stream(device)))
+
+
+_sh_factor_hook = None
+
+
+def set_sh_factor_hook(fn) -> None:
+    """fn(P, M, degree, means3D, dL_dsh) -> (factor_slot_multicast_ptr, campos_slot_multicast_ptr) or
+    None. When it returns pointers the backward multicasts the SH gradient factors instead of
+    writing dL_dsh; the hook's owner later fills dL_dsh with sh_grad_from_factors()."""
+    global _sh_factor_hook
+    _sh_factor_hook = fn
+
+
+def sh_grad_from_factors(P, D, M, world, means3D, campos_all_ptr: int, factors_all_ptr: int, dL_dsh,
+                         device) -> None:
+    with torch.cuda.device(device):
+        _check(lib().bgr_sh_grad_from_factors(int(P), int(D), int(M), int(world),
+                                              C.c_void_p(means3D.data_ptr()), C.c_void_p(campos_all_ptr),
+                                              C.c_void_p(factors_all_ptr), C.c_void_p(dL_dsh.data_ptr()),
+                                              _stream(device)))
 
 
 def nvls_visibility(radii, P: int, local_words_ptr: int, multicast_words_ptr: int, rank: int,

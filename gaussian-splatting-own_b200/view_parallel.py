@@ -68,47 +68,85 @@ def scatter_flat(flat: torch.Tensor, grads: Sequence[torch.Tensor]) -> None:
 
 
 class NvlsExchange:
-    """The gradient arena in symmetric (peer-mapped, multicast-bound) memory and the in-switch sum
-    over it, done by libbgr's own kernels (csrc/nvls_allreduce.cu). Construction is collective.
+    """The gradient arena in symmetric (peer-mapped, multicast-bound) memory and the exchange over
+    it, done by libbgr's own kernels (csrc/nvls_allreduce.cu, csrc/preprocess_bwd.cu).
+    Construction is collective; keep ONE instance per process for a given (P, M).
 
-    Exchange volume: the small leaves (means3D, opacity, scales: 7 floats/Gaussian) are summed
-    densely; rotations + sh (4 + 3M floats) only for Gaussians that at least one rank sees this
-    step (OR over ranks of radii > 0, itself reduced in the switch) — every other row is zero on
-    every rank already. At 3M Gaussians / 8 cameras the union is ~46 %, i.e. 370 MB instead of
-    708 MB cross the fabric."""
+    mode "factor" (default): dL/dsh[k] = basis_k(dir) * dL/dRGB is rank one per view, so the
+        backward kernel does not write the 3M floats of dL/dsh at all: it multicasts the 3 floats
+        of dL/dRGB per Gaussian (multimem.st, replicated by the NVSwitch into every GPU's copy of
+        slot [rank]) while it computes — the all-gather is fused into the producing kernel. After
+        one barrier every rank rebuilds sum_v basis(dir_v) x dL/dRGB_v locally (deterministic,
+        identical everywhere) and only the remaining 11 floats/Gaussian are summed in the switch.
+        Fabric traffic at 3M Gaussians, 8 GPUs: 36 MB out + 252 MB in (overlapped with the
+        backward) + a 132 MB in-switch sum, instead of a 708 MB all-reduce.
+    mode "rows": the small leaves densely, rotations + sh only for rows some rank sees.
+    mode "dense": the whole 59-float block in the switch."""
 
     NON_LEAF_FLOATS = 12   # means2D 3 + colors 3 + cov3D 6 precede the leaf block in the arena
     DENSE_FLOATS = 7       # means3D 3 + opacity 1 + scales 3
+    SMALL_FLOATS = 11      # ... + rotations 4: everything except sh
 
     def __init__(self, P: int, M: int, device, group: Optional[dist.ProcessGroup] = None,
-                 max_blocks: int = 296, sparse: bool = True):
+                 max_blocks: int = 296, mode: str = "factor"):
         import torch.distributed._symmetric_memory as symm_mem
         from diff_gaussian_rasterization import _C
         self._C = _C
         self.P, self.M, self.device = P, M, torch.device(device)
-        self.leaf_floats = 3 + 1 + 3 + 4 + 3 * M
+        self.leaf_floats = self.SMALL_FLOATS + 3 * M
         self.numel = P * (self.NON_LEAF_FLOATS + self.leaf_floats)
         self.max_blocks = max_blocks
-        self.words_off = (self.numel + 3) // 4 * 4
-        self.nwords = (P + 31) // 32
         grp = group if group is not None else dist.group.WORLD
-        self.buf = symm_mem.empty(self.words_off + (self.nwords + 3) // 4 * 4, dtype=torch.float32,
-                                  device=self.device)
+        world = dist.get_world_size(grp)
+        up4 = lambda n: (n + 3) // 4 * 4  # noqa: E731
+        self.words_off = up4(self.numel)
+        self.nwords = (P + 31) // 32
+        self.campos_off = self.words_off + up4(self.nwords)
+        self.factors_off = self.campos_off + 4 * world
+        aligned = P % 4 == 0
+        if mode == "factor" and not (aligned and M > 0):
+            mode = "rows"
+        if mode == "rows" and not (aligned and (3 * M) % 4 == 0 and 0 < 4 + 3 * M <= 64):
+            mode = "dense"
+        if mode not in ("factor", "rows", "dense"):
+            raise ValueError("mode must be 'factor', 'rows' or 'dense'")
+        self.mode = mode
+        total = self.factors_off + (world * P * 3 if mode == "factor" else 0)
+        self.buf = symm_mem.empty(total, dtype=torch.float32, device=self.device)
         self.hdl = symm_mem.rendezvous(self.buf, grp)
         if not self.hdl.multicast_ptr:
             raise RuntimeError("NVLink multicast (NVLS) is not available for this group")
         self.rank, self.world = self.hdl.rank, self.hdl.world_size
-        # row-sparse exchange needs 16-byte aligned rows: P % 4 == 0 and 3M % 4 == 0, rows <= 64 floats
-        self.sparse = bool(sparse and P % 4 == 0 and (3 * M) % 4 == 0 and 0 < 4 + 3 * M <= 64)
         self._have_mask = False
+        self._pending = None     # (D, means3D, dL_dsh) of the backward whose factors are in flight
         _C.set_grad_arena_provider(self._provide)
+        if mode == "factor":
+            _C.set_sh_factor_hook(self._factor_slots)
 
+    # ---- hooks called by _C.rasterize_gaussians_backward -------------------------------------
     def _provide(self, numel, dev):
         return self.buf[:self.numel] if (numel == self.numel and torch.device(dev) == self.buf.device) else None
 
+    def _factor_slots(self, P, M, degree, means3D, dL_dsh):
+        if P != self.P or M != self.M or means3D.device != self.buf.device:
+            return None
+        self._pending = (degree, means3D, dL_dsh)
+        mc = self.hdl.multicast_ptr
+        return (mc + 4 * (self.factors_off + self.rank * 3 * P), mc + 4 * (self.campos_off + 4 * self.rank))
+
+    @property
+    def sparse(self):
+        return self.mode == "rows"
+
+    @sparse.setter
+    def sparse(self, v):     # used by tests/dp_check.py to compare the modes on one instance
+        if self.mode != "factor":
+            self.mode = "rows" if v else "dense"
+
+    # ---- the exchange ------------------------------------------------------------------------
     def begin(self, radii: torch.Tensor) -> None:
-        """After the forward: visibility bits of this rank -> OR over ranks (in the switch)."""
-        if not self.sparse:
+        """After the forward (mode "rows" only): visibility bits -> OR over ranks in the switch."""
+        if self.mode != "rows":
             return
         mc, local = self.hdl.multicast_ptr + 4 * self.words_off, self.buf.data_ptr() + 4 * self.words_off
         self._C.nvls_visibility(radii, self.P, local, mc, self.rank, self.world, 0, self.device)
@@ -120,23 +158,32 @@ class NvlsExchange:
         """Sum of the leaf block across ranks, in place, on the current stream."""
         P, mc = self.P, self.hdl.multicast_ptr
         leaf0 = P * self.NON_LEAF_FLOATS
-        self.hdl.barrier(channel=0)        # every rank's backward (and visibility OR) is complete
-        if self.sparse and self._have_mask:
-            self._C.nvls_allreduce(mc, leaf0, P * self.DENSE_FLOATS, self.rank, self.world, self.device,
-                                   self.max_blocks)
+        red = lambda off, cnt: self._C.nvls_allreduce(mc, off, cnt, self.rank, self.world, self.device,  # noqa: E731
+                                                      self.max_blocks)
+        self.hdl.barrier(channel=0)        # every rank's backward (stores, multicasts) is complete
+        if self.mode == "factor" and self._pending is not None:
+            degree, means3D, dL_dsh = self._pending
+            red(leaf0, P * self.SMALL_FLOATS)
+            base = self.buf.data_ptr()
+            self._C.sh_grad_from_factors(P, degree, self.M, self.world, means3D,
+                                         base + 4 * self.campos_off, base + 4 * self.factors_off,
+                                         dL_dsh, self.device)
+            self._pending = None
+        elif self.mode == "rows" and self._have_mask:
+            red(leaf0, P * self.DENSE_FLOATS)
             rot0 = leaf0 + P * self.DENSE_FLOATS
             sh0 = rot0 + 4 * P
             self._C.nvls_allreduce_rows(mc + 4 * rot0, 4, mc + 4 * sh0, 3 * self.M,
                                         self.buf.data_ptr() + 4 * self.words_off, P, self.rank,
                                         self.world, self.device, self.max_blocks)
         else:
-            self._C.nvls_allreduce(mc, leaf0, P * self.leaf_floats, self.rank, self.world, self.device,
-                                   self.max_blocks)
+            red(leaf0, P * self.leaf_floats)
         self._have_mask = False
-        self.hdl.barrier(channel=0)        # every share has been broadcast to every rank
+        self.hdl.barrier(channel=0)        # sums broadcast everywhere; factor slots free for reuse
 
     def close(self):
         self._C.set_grad_arena_provider(None)
+        self._C.set_sh_factor_hook(None)
 
 
 class StepResult(NamedTuple):

@@ -106,6 +106,13 @@ typedef struct BgrBackwardArgs {
     float* dL_dscale;            /* [P,3]                                                   */
     float* dL_drot;              /* [P,4]                                                   */
     int    debug;
+    /* View-parallel path only (both NULL otherwise). dL/dsh = basis(dir) x dL/dRGB is rank one, so
+     * instead of writing dL_dsh the backward MULTICASTS (NVLink multimem.st) the clamp-masked
+     * dL/dRGB [P,3] into this rank's slot of a symmetric buffer on every GPU, and its camera
+     * position into its [4]-float slot; every rank then rebuilds the view-summed dL_dsh locally with
+     * bgr_sh_grad_from_factors. Needs P % 4 == 0. dL_dsh is not written by bgr_backward then.   */
+    float* sh_factor_multicast;  /* multicast address of slot [rank][P][3]                  */
+    float* campos_multicast;     /* multicast address of slot [rank][4]                     */
 } BgrBackwardArgs;
 
 /* Forward rasterization. Writes *num_rendered (total tile instances, the reference's return
@@ -158,6 +165,13 @@ BGR_API int bgr_inclusive_scan_u32(const uint32_t* in, uint32_t* out, size_t n, 
  * never waits on a peer). offset_floats must be a multiple of 4. */
 BGR_API int bgr_nvls_allreduce_f32(void* multicast_ptr, size_t offset_floats, size_t count_floats,
                                    int rank, int world, int max_blocks, void* stream);
+
+/* dL_dsh[i][k][:] = sum over the `world` views v of basis_k(dir_v(i)) * factors_all[v][i][:]
+ * (k < (D+1)^2, zero above), summed in view order on every rank => bit-identical replicas.
+ * campos_all: [world][4], factors_all: [world][P][3] (local addresses of the symmetric buffer). */
+BGR_API int bgr_sh_grad_from_factors(int P, int D, int M, int world, const float* means3D,
+                                     const float* campos_all, const float* factors_all, float* dL_dsh,
+                                     void* stream);
 
 /* Row-sparse variant. A Gaussian that no rank sees has an all-zero gradient row everywhere and need
  * not cross the fabric. phase 0: packs (radii > 0) into one bit per Gaussian in local_words (part of

@@ -1,6 +1,6 @@
 """Multi-GPU check of the view-parallel exchange (run under torchrun on >= 2 B200s; not a pytest —
 the round-end GPU suite has one GPU). Every rank renders its own camera; the leaf gradients summed
-by libbgr's in-switch kernels (dense and row-sparse) must equal the NCCL all-reduce of the same
+by libbgr's exchange kernels (factor multicast / row-sparse / dense) must equal the NCCL all-reduce of the same
 per-rank gradients, and be bit-identical on all ranks.
 
     python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tests/dp_check.py
@@ -42,11 +42,12 @@ def main():
     want = [g.clone() for g in base.grads]
     torch.cuda.synchronize()
 
-    ex = vp.NvlsExchange(P, 16, dev, sparse=True)
+    mode = sys.argv[2] if len(sys.argv) > 2 else "factor"
+    ex = vp.NvlsExchange(P, 16, dev, mode=mode)
     r = vp.ViewParallelRasterizer(exchange="nvls")
     r._nvls = ex
     peer = (rank + 1) % world
-    for sparse in (False, True):
+    for sparse in ((mode,) if mode == "factor" else (False, True)):
         ex.sparse = sparse
         for it in range(2):   # twice: the arena is reused
             res = r.step(scene, cam, bg, lambda c: dpix)
