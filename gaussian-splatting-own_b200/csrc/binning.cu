@@ -120,37 +120,74 @@ scan_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, size_t 
 // K2: one key per (Gaussian, touched tile), written at the Gaussian's scan offset in y-major,
 // x-minor order (rasterizer_impl.cu:98-108). Key layout: bgr_common.cuh KeyFormat.
 // --------------------------------------------------------------------------------------------
+// The 32 Gaussians of a warp own one contiguous run of the output (their scan offsets are
+// adjacent), so the warp writes that run cooperatively: output slot s is mapped back to its
+// source lane by a 5-step search over the warp's exclusive prefix, which makes every store
+// instruction cover 32 consecutive keys (the reference writes 12 B per instance at addresses
+// strided by each thread's own tile count).
 __global__ void __launch_bounds__(256)
 emit_keys_kernel(int P, const GaussRec* __restrict__ rec, const uint32_t* __restrict__ offsets,
                  const int* __restrict__ radii, int grid_x, int grid_y, KeyFormat kf,
                  uint64_t* __restrict__ keys, uint32_t* __restrict__ vals)
 {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= P) return;
-    const int radius = radii[idx];
-    if (!(radius > 0)) return;
-    uint32_t off = (idx == 0) ? 0u : offsets[idx - 1];
-    const float4 q0 = __ldg(&rec[idx].q0);
-    const float depth = __ldg(&rec[idx].q2).z;
-    uint2 rmin, rmax;
-    tile_rect(make_float2(q0.x, q0.y), radius, grid_x, grid_y, rmin, rmax);
-    const uint64_t drel = (uint64_t)(__float_as_uint(depth) - kf.depth_min);
-    if (kf.pairs) {
-        for (uint32_t y = rmin.y; y < rmax.y; ++y)
-            for (uint32_t x = rmin.x; x < rmax.x; ++x) {
-                const uint64_t tile = (uint64_t)(y * (uint32_t)grid_x + x);
-                keys[off] = (tile << kf.nb_depth) | drel;
-                vals[off] = (uint32_t)idx;
-                ++off;
-            }
-    } else {
-        const uint64_t low = (drel << kf.nb_idx) | (uint64_t)(uint32_t)idx;
-        for (uint32_t y = rmin.y; y < rmax.y; ++y)
-            for (uint32_t x = rmin.x; x < rmax.x; ++x) {
-                const uint64_t tile = (uint64_t)(y * (uint32_t)grid_x + x);
-                keys[off] = (tile << kf.tile_shift) | low;
-                ++off;
-            }
+    const int lane = threadIdx.x & 31;
+    uint32_t count = 0, minx = 0, miny = 0, width = 1;
+    uint64_t low = 0;
+    if (idx < P) {
+        const int radius = radii[idx];
+        if (radius > 0) {
+            const float4 q0 = __ldg(&rec[idx].q0);
+            const float depth = __ldg(&rec[idx].q2).z;
+            uint2 rmin, rmax;
+            tile_rect(make_float2(q0.x, q0.y), radius, grid_x, grid_y, rmin, rmax);
+            minx = rmin.x; miny = rmin.y;
+            width = rmax.x - rmin.x;
+            count = width * (rmax.y - rmin.y);
+            const uint64_t drel = (uint64_t)(__float_as_uint(depth) - kf.depth_min);
+            low = kf.pairs ? drel : ((drel << kf.nb_idx) | (uint64_t)(uint32_t)idx);
+            if (width == 0) width = 1;
+        }
+    }
+    // exclusive prefix of the counts inside the warp
+    uint32_t incl = count;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += t;
+    }
+    const uint32_t excl = incl - count;
+    const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+    if (total == 0) return;
+    // first output slot of the warp = scan offset preceding its first Gaussian
+    const int first_idx = idx - lane;
+    uint32_t warp_off = 0;
+    if (lane == 0) warp_off = (first_idx == 0) ? 0u : offsets[first_idx - 1];
+    warp_off = __shfl_sync(0xffffffffu, warp_off, 0);
+
+    for (uint32_t base = 0; base < total; base += 32) {
+        const uint32_t s = base + lane;
+        // largest lane l with excl[l] <= s (zero-count lanes share a prefix with their successor;
+        // taking the largest such lane lands on the one that actually owns the slot)
+        int src = 0;
+#pragma unroll
+        for (int step = 16; step > 0; step >>= 1) {
+            const int cand = src + step;
+            const uint32_t e = __shfl_sync(0xffffffffu, excl, cand & 31);
+            if (cand < 32 && e <= s) src = cand;
+        }
+        const uint32_t e_src = __shfl_sync(0xffffffffu, excl, src);
+        const uint32_t w_src = __shfl_sync(0xffffffffu, width, src);
+        const uint32_t x_src = __shfl_sync(0xffffffffu, minx, src);
+        const uint32_t y_src = __shfl_sync(0xffffffffu, miny, src);
+        const uint64_t low_src = __shfl_sync(0xffffffffu, low, src);
+        if (s < total) {
+            const uint32_t local = s - e_src;
+            const uint32_t ty = local / w_src, tx = local - ty * w_src;
+            const uint64_t tile = (uint64_t)((y_src + ty) * (uint32_t)grid_x + x_src + tx);
+            keys[warp_off + s] = (tile << kf.tile_shift) | low_src;
+            if (kf.pairs) vals[warp_off + s] = (uint32_t)(first_idx + src);
+        }
     }
 }
 

@@ -246,35 +246,40 @@ __device__ __forceinline__ V3 preprocess_backward_body(const PreprocessBackwardP
 
         V3 dRGBdx = v3(0.f, 0.f, 0.f), dRGBdy = v3(0.f, 0.f, 0.f), dRGBdz = v3(0.f, 0.f, 0.f);
         if (kVecSH) {
-            // 48 floats in, 48 floats out, as 12 + 12 128-bit accesses
+            // 48 floats in, 48 floats out, as 12 + 12 128-bit accesses, four coefficients
+            // (3 float4) at a time so that only 24 floats are live instead of 96
             const float4* src = reinterpret_cast<const float4*>(p.shs) + i * 12;
             float4* dst = reinterpret_cast<float4*>(p.dL_dsh) + i * 12;
-            float sh[48], out[48];
-            const int nvec = (3 * ncoef + 3) >> 2;
 #pragma unroll
-            for (int k = 0; k < 12; ++k) {
-                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (k < nvec) v = __ldg(src + k);
-                sh[4 * k] = v.x; sh[4 * k + 1] = v.y; sh[4 * k + 2] = v.z; sh[4 * k + 3] = v.w;
-            }
+            for (int c = 0; c < 4; ++c) {
+                float sh[12], out[12];
+                const bool live = 4 * c < ncoef;
 #pragma unroll
-            for (int k = 0; k < 16; ++k) {
-                const bool on = k < ncoef;
-                const float bk = on ? bas[k] : 0.f;
+                for (int q = 0; q < 3; ++q) {
+                    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (live) v = __ldg(src + 3 * c + q);
+                    sh[4 * q] = v.x; sh[4 * q + 1] = v.y; sh[4 * q + 2] = v.z; sh[4 * q + 3] = v.w;
+                }
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk) {
+                    const int k = 4 * c + kk;
+                    const bool on = k < ncoef;
+                    const float bk = on ? bas[k] : 0.f;
+                    if (!kFactor) {
+                        out[3 * kk] = bk * dRGB.x; out[3 * kk + 1] = bk * dRGB.y; out[3 * kk + 2] = bk * dRGB.z;
+                    }
+                    if (on && k > 0) {
+                        const V3 s = v3(sh[3 * kk], sh[3 * kk + 1], sh[3 * kk + 2]);
+                        dRGBdx = dRGBdx + bx[k] * s;
+                        dRGBdy = dRGBdy + by[k] * s;
+                        dRGBdz = dRGBdz + bz[k] * s;
+                    }
+                }
                 if (!kFactor) {
-                    out[3 * k] = bk * dRGB.x; out[3 * k + 1] = bk * dRGB.y; out[3 * k + 2] = bk * dRGB.z;
-                }
-                if (on && k > 0) {
-                    const V3 s = v3(sh[3 * k], sh[3 * k + 1], sh[3 * k + 2]);
-                    dRGBdx = dRGBdx + bx[k] * s;
-                    dRGBdy = dRGBdy + by[k] * s;
-                    dRGBdz = dRGBdz + bz[k] * s;
-                }
-            }
-            if (!kFactor) {
 #pragma unroll
-                for (int k = 0; k < 12; ++k)
-                    dst[k] = make_float4(out[4 * k], out[4 * k + 1], out[4 * k + 2], out[4 * k + 3]);
+                    for (int q = 0; q < 3; ++q)
+                        dst[3 * c + q] = make_float4(out[4 * q], out[4 * q + 1], out[4 * q + 2], out[4 * q + 3]);
+                }
             }
         } else {
             const float* src = p.shs + i * p.M * 3;

@@ -27,9 +27,12 @@ render_backward_kernel(int W, int H, const uint2* __restrict__ ranges,
                        const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix,
                        float* __restrict__ acc)
 {
-    __shared__ float4 s_geo[RENDER_THREADS];  // x, y, conic.x, conic.y
-    __shared__ float4 s_opa[RENDER_THREADS];  // conic.z, thr, opacity, list position (bits)
-    __shared__ float4 s_col[RENDER_THREADS];  // r, g, b, Gaussian id (bits)
+    __shared__ float4 s_rec[3 * RENDER_THREADS];   // planes: geo | opa | col (see lds128)
+    float4* const s_geo = s_rec;
+    float4* const s_opa = s_rec + RENDER_THREADS;
+    float4* const s_col = s_rec + 2 * RENDER_THREADS;
+    uint32_t s_base;   // opaque to the optimiser so that it stays in a register across the loops
+    asm volatile("mov.u32 %0, %1;" : "=r"(s_base) : "r"((uint32_t)__cvta_generic_to_shared(s_rec)));
     __shared__ uint32_t s_warp_count[RENDER_WARPS];
     __shared__ uint32_t s_warp_max[RENDER_WARPS];
 
@@ -131,8 +134,9 @@ render_backward_kernel(int W, int H, const uint2* __restrict__ ranges,
         while (hits) {
             const int j = base + __ffs(hits) - 1;
             hits &= hits - 1;
-            const float4 a = s_geo[j];
-            const float4 o = s_opa[j];
+            const uint32_t ja = s_base + 16u * (uint32_t)j;
+            const float4 a = lds128(ja);
+            const float4 o = lds128(ja + PLANE_BYTES);
             const uint32_t pos_in_list = __float_as_uint(o.w);
             bool valid = pos_in_list < last_contributor;  // false for pixels outside the image
             const float dx = a.x - pixfx;
@@ -144,7 +148,7 @@ render_backward_kernel(int W, int H, const uint2* __restrict__ ranges,
             const float alpha = fminf(0.99f, o.z * G);
             valid = valid && !(alpha < 1.0f / 255.0f);
             if (!__any_sync(0xffffffffu, valid)) continue;
-            const float4 c = s_col[j];
+            const float4 c = lds128(ja + 2 * PLANE_BYTES);
             // names used by the gradient block below: b = {conic.z, opacity, r, g}, c.x = blue
             const float4 b = make_float4(o.x, o.z, c.x, c.y);
             const float cblue = c.z;

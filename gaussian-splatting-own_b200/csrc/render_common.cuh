@@ -17,6 +17,21 @@ __device__ __forceinline__ void tile_pixel(int tid, int& lx, int& ly)
     ly = ((warp >> 1) << 2) | (lane >> 3);
 }
 
+// 128-bit shared-memory load from a 32-bit shared-window address. The staged records of both render
+// kernels live in ONE float4 array [3][RENDER_THREADS] (geo | opa | col), so the address of entry j is
+// base + 16*j and the three planes are immediate offsets of the same register: the hot loops then
+// issue one address computation per splat instead of recomputing the shared window base per access
+// (which is what nvcc emitted for three separate __shared__ arrays).
+__device__ __forceinline__ float4 lds128(uint32_t addr)
+{
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "r"(addr));
+    return v;
+}
+constexpr uint32_t PLANE_BYTES = RENDER_THREADS * 16;
+
 // Exactly the reference's evaluation order for the Gaussian exponent (forward.cu:335, SASS shape in
 // SURVEY.md A.5): power = -0.5*(cx*dx*dx + cz*dy*dy) - cy*dx*dy with
 //   t = (cz*dy)*dy, u = cx*dx, q = fma(u,dx,t), v = (cy*dx)*dy, power = fma(-0.5,q,-v).

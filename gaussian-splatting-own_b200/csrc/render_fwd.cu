@@ -38,9 +38,12 @@ render_forward_kernel(int W, int H, const uint2* __restrict__ ranges,
     //   s_geo : x, y, conic.x, conic.y            (culling test + every pair)
     //   s_opa : conic.z, thr, opacity, list pos+1 (culling test + every pair)
     //   s_col : r, g, b                            (only pairs that blend)
-    __shared__ float4 s_geo[RENDER_THREADS];
-    __shared__ float4 s_opa[RENDER_THREADS];
-    __shared__ float4 s_col[RENDER_THREADS];
+    __shared__ float4 s_rec[3 * RENDER_THREADS];   // planes: geo | opa | col (see lds128)
+    float4* const s_geo = s_rec;
+    float4* const s_opa = s_rec + RENDER_THREADS;
+    float4* const s_col = s_rec + 2 * RENDER_THREADS;
+    uint32_t s_base;   // opaque to the optimiser so that it stays in a register across the loops
+    asm volatile("mov.u32 %0, %1;" : "=r"(s_base) : "r"((uint32_t)__cvta_generic_to_shared(s_rec)));
     __shared__ uint32_t s_warp_count[RENDER_WARPS];
     unsigned long long st_kept = 0, st_exam = 0, st_exp = 0, st_blend = 0;
 
@@ -122,8 +125,9 @@ render_forward_kernel(int W, int H, const uint2* __restrict__ ranges,
                 const int j = base + __ffs(hits) - 1;
                 hits &= hits - 1;
                 if (done) continue;
-                const float4 a = s_geo[j];
-                const float4 b = s_opa[j];
+                const uint32_t ja = s_base + 16u * (uint32_t)j;
+                const float4 a = lds128(ja);
+                const float4 b = lds128(ja + PLANE_BYTES);
                 const float dx = a.x - pixfx;
                 const float dy = a.y - pixfy;
                 const float power = gauss_power(a.z, a.w, b.x, dx, dy);
@@ -137,7 +141,7 @@ render_forward_kernel(int W, int H, const uint2* __restrict__ ranges,
                     done = true;
                     continue;
                 }
-                const float4 c = s_col[j];
+                const float4 c = lds128(ja + 2 * PLANE_BYTES);
                 C0 = __fmaf_rn(__fmul_rn(c.x, alpha), T, C0);
                 C1 = __fmaf_rn(__fmul_rn(c.y, alpha), T, C1);
                 C2 = __fmaf_rn(__fmul_rn(c.z, alpha), T, C2);

@@ -119,6 +119,7 @@ class NvlsExchange:
         self.rank, self.world = self.hdl.rank, self.hdl.world_size
         self._have_mask = False
         self._pending = None     # (D, means3D, dL_dsh) of the backward whose factors are in flight
+        self._side = None
         _C.set_grad_arena_provider(self._provide)
         if mode == "factor":
             _C.set_sh_factor_hook(self._factor_slots)
@@ -163,11 +164,18 @@ class NvlsExchange:
         self.hdl.barrier(channel=0)        # every rank's backward (stores, multicasts) is complete
         if self.mode == "factor" and self._pending is not None:
             degree, means3D, dL_dsh = self._pending
-            red(leaf0, P * self.SMALL_FLOATS)
             base = self.buf.data_ptr()
-            self._C.sh_grad_from_factors(P, degree, self.M, self.world, means3D,
-                                         base + 4 * self.campos_off, base + 4 * self.factors_off,
-                                         dL_dsh, self.device)
+            # the local rebuild of dL_dsh (HBM-bound) runs beside the in-switch sum (NVLink-bound)
+            cur = torch.cuda.current_stream(self.device)
+            if self._side is None:
+                self._side = torch.cuda.Stream(self.device)
+            self._side.wait_stream(cur)
+            with torch.cuda.stream(self._side):
+                self._C.sh_grad_from_factors(P, degree, self.M, self.world, means3D,
+                                             base + 4 * self.campos_off, base + 4 * self.factors_off,
+                                             dL_dsh, self.device)
+            red(leaf0, P * self.SMALL_FLOATS)
+            cur.wait_stream(self._side)
             self._pending = None
         elif self.mode == "rows" and self._have_mask:
             red(leaf0, P * self.DENSE_FLOATS)
