@@ -250,16 +250,18 @@ __device__ __forceinline__ V3 preprocess_backward_body(const PreprocessBackwardP
             // (3 float4) at a time so that only 24 floats are live instead of 96
             const float4* src = reinterpret_cast<const float4*>(p.shs) + i * 12;
             float4* dst = reinterpret_cast<float4*>(p.dL_dsh) + i * 12;
+            // all twelve loads are issued up front (memory-level parallelism) ...
+            float sh[48];
+#pragma unroll
+            for (int q = 0; q < 12; ++q) {
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (4 * (q / 3) < ncoef) v = __ldg(src + q);
+                sh[4 * q] = v.x; sh[4 * q + 1] = v.y; sh[4 * q + 2] = v.z; sh[4 * q + 3] = v.w;
+            }
+            // ... the outputs are produced and stored four coefficients at a time
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
-                float sh[12], out[12];
-                const bool live = 4 * c < ncoef;
-#pragma unroll
-                for (int q = 0; q < 3; ++q) {
-                    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (live) v = __ldg(src + 3 * c + q);
-                    sh[4 * q] = v.x; sh[4 * q + 1] = v.y; sh[4 * q + 2] = v.z; sh[4 * q + 3] = v.w;
-                }
+                float out[12];
 #pragma unroll
                 for (int kk = 0; kk < 4; ++kk) {
                     const int k = 4 * c + kk;
@@ -269,7 +271,7 @@ __device__ __forceinline__ V3 preprocess_backward_body(const PreprocessBackwardP
                         out[3 * kk] = bk * dRGB.x; out[3 * kk + 1] = bk * dRGB.y; out[3 * kk + 2] = bk * dRGB.z;
                     }
                     if (on && k > 0) {
-                        const V3 s = v3(sh[3 * kk], sh[3 * kk + 1], sh[3 * kk + 2]);
+                        const V3 s = v3(sh[3 * k], sh[3 * k + 1], sh[3 * k + 2]);
                         dRGBdx = dRGBdx + bx[k] * s;
                         dRGBdy = dRGBdy + by[k] * s;
                         dRGBdz = dRGBdz + bz[k] * s;

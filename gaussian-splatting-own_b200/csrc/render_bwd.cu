@@ -157,7 +157,13 @@ render_backward_kernel(int W, int H, const uint2* __restrict__ ranges,
                   v8 = 0.f;
             if (valid) {
                 const float one_m_alpha = 1.f - alpha;
-                T = T / one_m_alpha;
+                // 1/(1-alpha) once (MUFU.RCP + one Newton step, <= 1 ulp; 1-alpha is in [0.01, 1])
+                // instead of the reference's two IEEE divisions: gradients are tolerance-level
+                // and this is well inside the reference's own atomic-ordering noise.
+                float rcp_oma;
+                asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rcp_oma) : "f"(one_m_alpha));
+                rcp_oma = __fmaf_rn(rcp_oma, __fmaf_rn(-one_m_alpha, rcp_oma, 1.0f), rcp_oma);
+                T = T * rcp_oma;
                 const float dchannel_dcolor = alpha * T;
                 float dL_dalpha = 0.0f;
                 const float one_m_last = 1.f - last_alpha;
@@ -172,7 +178,7 @@ render_backward_kernel(int W, int H, const uint2* __restrict__ ranges,
                 dL_dalpha += (cblue - accum2) * g2;
                 dL_dalpha *= T;
                 last_alpha = alpha;
-                dL_dalpha += (-T_final / one_m_alpha) * bg_dot_dpixel;
+                dL_dalpha += (-T_final * rcp_oma) * bg_dot_dpixel;
 
                 const float dL_dG = b.y * dL_dalpha;
                 const float gdx = G * dx;
