@@ -210,10 +210,17 @@ def make_e2e_step(backend, wl, world, impl):
     loss_host = torch.zeros((), dtype=torch.float32).pin_memory()
     leaves = {k: v.clone().requires_grad_(True) for k, v in wl.scene.items()}
     h2d = cam_host.numel() * 4 + w_host.numel() * 4
+    # The loss weights are first needed after the forward: their copy runs on a second stream
+    # under the forward kernels (both arms use this harness). The step ends with a synchronize,
+    # so the next step's copy cannot overtake this step's reads.
+    copy_stream = torch.cuda.Stream(device=dev)
+    w_ready = torch.cuda.Event()
 
     def step():
         cam_dev.copy_(cam_host, non_blocking=True)
-        w_dev.copy_(w_host, non_blocking=True)
+        with torch.cuda.stream(copy_stream):
+            w_dev.copy_(w_host, non_blocking=True)
+            w_ready.record(copy_stream)
         for t in leaves.values():
             t.grad = None
         settings = dgr.GaussianRasterizationSettings(
@@ -229,6 +236,7 @@ def make_e2e_step(backend, wl, world, impl):
         nvls = getattr(make_native_step, "nvls", None) if world > 1 else None
         if nvls is not None:
             nvls.begin(radii_)
+        torch.cuda.current_stream().wait_event(w_ready)
         loss = (color * w_dev).sum()
         loss.backward()
         if world > 1:
