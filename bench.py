@@ -54,6 +54,10 @@ def parse_args():
     ap.add_argument("--res", choices=("800x800", "1080p", "4k"), default="1080p")
     ap.add_argument("--skip-cpu-baseline", action="store_true")
     ap.add_argument("--skip-e2e", action="store_true")
+    ap.add_argument("--chunks", type=int, default=1,
+                    help="N > 1, --exchange nvls: Gaussian ranges the backward preprocess is pipelined "
+                         "against the exchange in (1 = exchange after the backward)")
+    ap.add_argument("--nvls-blocks", type=int, default=296, help="CTAs of the in-switch sum kernel")
     ap.add_argument("--exchange", choices=("nvls", "nvls-rows", "nvls-dense", "nccl"), default="nvls",
                     help="N > 1, ours: in-switch multimem kernel of libbgr (default) or ncclAllReduce")
     return ap.parse_args()
@@ -158,14 +162,15 @@ class Workload:
                 binning, img, False)
 
 
-def make_native_step(backend, wl, world, impl, exchange="nccl"):
+def make_native_step(backend, wl, world, impl, exchange="nccl", chunks=1, nvls_blocks=296):
     """forward + backward through the backend's `_C`-signature calls; N > 1 adds the all-reduce."""
     import torch.distributed as dist
     import view_parallel as vp
     nvls = None
     if world > 1 and impl == "ours" and exchange.startswith("nvls"):
         nvls = vp.NvlsExchange(wl.P, 16, wl.device,
-                               mode={"nvls": "factor", "nvls-rows": "rows", "nvls-dense": "dense"}[exchange])
+                               mode={"nvls": "factor", "nvls-rows": "rows", "nvls-dense": "dense"}[exchange],
+                               chunks=chunks, max_blocks=nvls_blocks)
     make_native_step.nvls = nvls
 
     def step():
@@ -355,6 +360,36 @@ def roofline_report(backend, wl, steps, device):
     return roof, stages, (max(hbm, key=lambda s: s["ms"]) if hbm else None), workload_stats, peak_src
 
 
+def dp_breakdown(backend, wl, impl, world, device, ms_per_step):
+    """N > 1 diagnostic, outside the timed region: every rank times its own view WITHOUT the
+    exchange (private gradient buffers, plain backward kernel). The step time is bounded below by
+    the slowest view; what is left is the exchange (barriers, multicast, in-switch sum, rebuild)."""
+    import torch.distributed as dist
+    if impl == "ours":
+        backend.set_grad_arena_provider(None)
+        backend.set_sh_factor_hook(None)
+    n = 20
+    for _ in range(3):
+        out = backend.rasterize_gaussians(*wl.fwd_args())
+        backend.rasterize_gaussians_backward(*wl.bwd_args(out))
+    torch.cuda.synchronize(device)
+    dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(n):
+        out = backend.rasterize_gaussians(*wl.fwd_args())
+        backend.rasterize_gaussians_backward(*wl.bwd_args(out))
+    e1.record()
+    torch.cuda.synchronize(device)
+    mine = torch.tensor([e0.elapsed_time(e1) / n], device=device)
+    every = [torch.zeros_like(mine) for _ in range(world)]
+    dist.all_gather(every, mine)
+    local = [round(float(t), 4) for t in every]
+    return {"local_ms_per_rank": local, "slowest_view_ms": max(local),
+            "exchange_ms": round(ms_per_step - max(local), 4),
+            "note": "local = this rank's view, forward + backward without any exchange"}
+
+
 def cpu_baseline(wl):
     """One view (forward + backward) of the SAME workload on the host cores with the plain-C
     oracle port (the reference has no CPU rasterizer)."""
@@ -397,7 +432,7 @@ def main():
         dist.init_process_group("nccl", device_id=device)
 
     wl = Workload(args, rank, device)
-    native = make_native_step(backend, wl, world, args.impl, args.exchange)
+    native = make_native_step(backend, wl, world, args.impl, args.exchange, args.chunks, args.nvls_blocks)
 
     launches0 = backend.launch_count() if args.impl == "ours" else 0
     native()  # first call: lazy init (pinned control block, func attributes)
@@ -449,6 +484,17 @@ def main():
                              "the reference has no CPU implementation of this path")
         line["cpu_baseline"] = {"value": line["value"], "unit": "views/s", "cores": 0, "kind": "reference",
                                 "sample": "not a CPU run: reference CUDA extension, same workload and harness"}
+    if world > 1:
+        nvls = getattr(make_native_step, "nvls", None)
+        pieces = None
+        if nvls is not None:      # exchange pieces, outside the timed region
+            nvls.profile = True
+            for _ in range(20):
+                native()
+            pieces = nvls.profile_report()
+            nvls.profile = False
+        line["dp"] = dp_breakdown(backend, wl, args.impl, world, device, ms_per_step)
+        line["dp"]["exchange_pieces_ms_rank0"] = pieces
     if rank == 0:
         print(json.dumps(line))
     if world > 1:

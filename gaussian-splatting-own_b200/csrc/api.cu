@@ -331,14 +331,29 @@ BGR_API int bgr_backward(const BgrBackwardArgs* a, void* stream_v)
     const uint2* ranges = reinterpret_cast<const uint2*>(img + IL.ranges);
     float* acc = static_cast<float*>(a->scratch);
 
+    // stages == 0: everything. Otherwise the caller splits the call: ACCUMULATE once, then
+    // PREPROCESS over consecutive Gaussian ranges, so that it can exchange the gradients of one
+    // range while the next is being computed.
+    const bool do_accumulate = a->stages == 0 || (a->stages & BGR_BACKWARD_ACCUMULATE) != 0;
+    const bool do_preprocess = a->stages == 0 || (a->stages & BGR_BACKWARD_PREPROCESS) != 0;
+    int begin = 0, end = a->P;
+    if (a->stages != 0 && do_preprocess) {
+        begin = a->gaussian_begin;
+        end = a->gaussian_end;
+        if (begin < 0 || end > a->P || begin > end)
+            return fail(BGR_ERR_INVALID_ARG, "bad Gaussian range");
+    }
+
     int rc;
+    if (do_accumulate) {
     g_timer.begin(ST_ACC_CLEAR, s);
     if ((rc = check_cuda(cudaMemsetAsync(acc, 0, (size_t)a->P * ACC_STRIDE * sizeof(float), s),
                          "memset accumulators")))
         return rc;
     g_timer.end(ST_ACC_CLEAR, s);
+    }
 
-    if (a->R > 0) {
+    if (do_accumulate && a->R > 0) {
         const uint32_t* point_list = reinterpret_cast<const uint32_t*>(bin + BL.point_list);
         g_timer.begin(ST_RENDER_BWD, s);
         launch_render_backward(a->width, a->height, ranges, point_list, rec, nullptr, a->background,
@@ -347,7 +362,9 @@ BGR_API int bgr_backward(const BgrBackwardArgs* a, void* stream_v)
         if ((rc = stage_check(debug, s, "render backward"))) return rc;
     }
 
+    if (!do_preprocess) return BGR_OK;
     PreprocessBackwardParams pb;
+    pb.begin = begin; pb.end = end;
     pb.P = a->P; pb.D = a->D; pb.M = a->M; pb.W = a->width; pb.H = a->height;
     pb.means3D = a->means3D; pb.radii = a->radii; pb.shs = a->shs; pb.scales = a->scales;
     pb.rotations = a->rotations; pb.scale_modifier = a->scale_modifier;
@@ -362,10 +379,11 @@ BGR_API int bgr_backward(const BgrBackwardArgs* a, void* stream_v)
     pb.dL_dscale = a->dL_dscale; pb.dL_drot = a->dL_drot;
     pb.factor_mc = a->sh_factor_multicast; pb.campos_mc = a->campos_multicast;
     if (pb.factor_mc != nullptr) {
-        if (pb.shs == nullptr || pb.campos_mc == nullptr || (a->P & 3) != 0 ||
-            (reinterpret_cast<uintptr_t>(pb.factor_mc) & 15) != 0)
+        if (pb.shs == nullptr || pb.campos_mc == nullptr || (a->P & 3) != 0 || (begin & 3) != 0 ||
+            (end & 3) != 0 || (reinterpret_cast<uintptr_t>(pb.factor_mc) & 15) != 0)
             return fail(BGR_ERR_INVALID_ARG,
-                        "SH factor multicast needs SHs, a camera slot, P % 4 == 0 and a 16-byte aligned slot");
+                        "SH factor multicast needs SHs, a camera slot, P and the range bounds % 4 == 0 "
+                        "and a 16-byte aligned slot");
     } else if (pb.shs != nullptr && pb.dL_dsh == nullptr) {
         return fail(BGR_ERR_INVALID_ARG, "dL_dsh is NULL although SHs were given");
     }
@@ -429,18 +447,42 @@ BGR_API int bgr_nvls_allreduce_f32(void* multicast_ptr, size_t offset_floats, si
     return stage_check(false, s, "nvls all-reduce");
 }
 
+BGR_API int bgr_nvls_allreduce_segments_f32(void* multicast_ptr, int nseg, const size_t* offsets_floats,
+                                            const size_t* counts_floats, int rank, int world,
+                                            int max_blocks, void* stream_v)
+{
+    cudaStream_t s = static_cast<cudaStream_t>(stream_v);
+    if (nseg > 0 && (offsets_floats == nullptr || counts_floats == nullptr))
+        return fail(BGR_ERR_INVALID_ARG, "NULL segment table");
+    if (bgr::launch_nvls_allreduce_segments(multicast_ptr, nseg, offsets_floats, counts_floats, rank,
+                                            world, max_blocks, s) != 0)
+        return fail(BGR_ERR_INVALID_ARG, "bad NVLS segment all-reduce arguments (NULL multicast pointer, rank, "
+                                         "more than 4 segments, or offsets/counts not multiples of 4 floats)");
+    return stage_check(false, s, "nvls segment all-reduce");
+}
+
+BGR_API int bgr_sh_grad_from_factors_range(int P, int begin, int end, int D, int M, int world,
+                                           const float* means3D, const float* campos_all,
+                                           const float* factors_all, float* dL_dsh, void* stream_v)
+{
+    cudaStream_t s = static_cast<cudaStream_t>(stream_v);
+    if (P < 0 || D < 0 || D > 3 || M < (D + 1) * (D + 1) || world <= 0 || begin < 0 || end > P ||
+        begin > end)
+        return fail(BGR_ERR_INVALID_ARG, "bad sizes");
+    if (begin == end) return BGR_OK;
+    if (means3D == nullptr || campos_all == nullptr || factors_all == nullptr || dL_dsh == nullptr)
+        return fail(BGR_ERR_INVALID_ARG, "required pointer is NULL");
+    bgr::launch_sh_grad_from_factors(P, begin, end, D, M, world, means3D, campos_all, factors_all,
+                                     dL_dsh, s);
+    return stage_check(false, s, "sh gradient from factors");
+}
+
 BGR_API int bgr_sh_grad_from_factors(int P, int D, int M, int world, const float* means3D,
                                      const float* campos_all, const float* factors_all, float* dL_dsh,
                                      void* stream_v)
 {
-    cudaStream_t s = static_cast<cudaStream_t>(stream_v);
-    if (P < 0 || D < 0 || D > 3 || M < (D + 1) * (D + 1) || world <= 0)
-        return fail(BGR_ERR_INVALID_ARG, "bad sizes");
-    if (P == 0) return BGR_OK;
-    if (means3D == nullptr || campos_all == nullptr || factors_all == nullptr || dL_dsh == nullptr)
-        return fail(BGR_ERR_INVALID_ARG, "required pointer is NULL");
-    bgr::launch_sh_grad_from_factors(P, D, M, world, means3D, campos_all, factors_all, dL_dsh, s);
-    return stage_check(false, s, "sh gradient from factors");
+    return bgr_sh_grad_from_factors_range(P, 0, P, D, M, world, means3D, campos_all, factors_all,
+                                          dL_dsh, stream_v);
 }
 
 BGR_API int bgr_nvls_visibility_or(const int* radii, int P, uint32_t* local_words,

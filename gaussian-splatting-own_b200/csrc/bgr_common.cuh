@@ -192,6 +192,9 @@ int launch_nvls_allreduce(void* multicast_ptr, size_t offset, size_t count, int 
                           int max_blocks, cudaStream_t s);
 
 void launch_pack_visibility(const int* radii, int P, uint32_t* words, cudaStream_t s);
+int launch_nvls_allreduce_segments(void* multicast_ptr, int nseg, const size_t* offsets,
+                                   const size_t* counts, int rank, int world, int max_blocks,
+                                   cudaStream_t s);
 int launch_nvls_or(void* multicast_words, size_t nwords, int rank, int world, cudaStream_t s);
 int launch_nvls_sparse_rows(void* mc_a, int vecs_a, void* mc_b, int vecs_b, const uint32_t* vis_words,
                             size_t rows, int rank, int world, int max_blocks, cudaStream_t s);
@@ -209,10 +212,13 @@ struct PreprocessBackwardParams {
     // view-parallel path: multicast address of this rank's factor slot [P][3] and of its camera
     // position slot [4] (nullptr => write dL_dsh normally)
     float* factor_mc; float* campos_mc;
+    // Gaussian range [begin, end) handled by this launch (the whole scene unless the caller
+    // pipelines the kernel against the gradient exchange chunk by chunk)
+    int begin, end;
 };
 void launch_preprocess_backward(const PreprocessBackwardParams& p, cudaStream_t s);
-void launch_sh_grad_from_factors(int P, int D, int M, int world, const float* means3D,
-                                 const float* campos_all, const float* factors_all, float* dL_dsh,
-                                 cudaStream_t s);
+void launch_sh_grad_from_factors(int P, int begin, int end, int D, int M, int world,
+                                 const float* means3D, const float* campos_all,
+                                 const float* factors_all, float* dL_dsh, cudaStream_t s);
 
 }  // namespace bgr

@@ -68,6 +68,35 @@ nvls_allreduce_kernel(float* __restrict__ mc, size_t vec_begin, size_t vec_end, 
     __threadfence_system();
 }
 
+// Up to four disjoint ranges in ONE launch: the Gaussian range [p0, p1) of the structure-of-arrays
+// leaf block (means3D | opacity | scales | rotations) is four short ranges, reduced as soon as the
+// backward preprocess has produced that chunk on every rank (view_parallel.py pipelines them).
+struct NvlsSegments {
+    size_t begin[4];   // this rank's share of each range, in float4 units from the multicast base
+    size_t end[4];
+};
+
+__global__ void __launch_bounds__(NVLS_THREADS)
+nvls_allreduce_segments_kernel(float* __restrict__ mc, NvlsSegments seg)
+{
+    float4* mc4 = reinterpret_cast<float4*>(mc);
+    const size_t stride = (size_t)gridDim.x * NVLS_THREADS;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const size_t vec_end = seg.end[k];
+        size_t i = seg.begin[k] + (size_t)blockIdx.x * NVLS_THREADS + threadIdx.x;
+        for (; i + (NVLS_UNROLL - 1) * stride < vec_end; i += NVLS_UNROLL * stride) {
+            float4 v[NVLS_UNROLL];
+#pragma unroll
+            for (int u = 0; u < NVLS_UNROLL; ++u) v[u] = mm_ld_reduce(mc4 + i + u * stride);
+#pragma unroll
+            for (int u = 0; u < NVLS_UNROLL; ++u) mm_st(mc4 + i + u * stride, v[u]);
+        }
+        for (; i < vec_end; i += stride) mm_st(mc4 + i, mm_ld_reduce(mc4 + i));
+    }
+    __threadfence_system();
+}
+
 // ---- row-sparse variant -----------------------------------------------------------------------
 // A Gaussian that no rank sees (radii == 0 everywhere) has an all-zero gradient row on every rank,
 // so its row need not cross the fabric at all. vis_words holds one bit per Gaussian: the OR over
@@ -192,6 +221,35 @@ int launch_nvls_allreduce(void* multicast_ptr, size_t offset, size_t count, int 
     blocks = std::max<size_t>(1, std::min<size_t>(blocks, (size_t)std::max(1, max_blocks)));
     ++g_kernel_launches;
     nvls_allreduce_kernel<<<(unsigned)blocks, NVLS_THREADS, 0, s>>>(mc, vb, ve, tb, te);
+    return 0;
+}
+
+int launch_nvls_allreduce_segments(void* multicast_ptr, int nseg, const size_t* offsets,
+                                   const size_t* counts, int rank, int world, int max_blocks,
+                                   cudaStream_t s)
+{
+    if (multicast_ptr == nullptr || world <= 0 || rank < 0 || rank >= world || nseg < 0 || nseg > 4)
+        return -1;
+    NvlsSegments seg;
+    size_t work = 0;
+    for (int k = 0; k < 4; ++k) {
+        seg.begin[k] = seg.end[k] = 0;
+        if (k >= nseg) continue;
+        if ((offsets[k] & 3) != 0 || (counts[k] & 3) != 0) return -1;
+        const size_t nvec = counts[k] / 4, first = offsets[k] / 4;
+        const size_t per = (nvec + world - 1) / world;
+        const size_t vb = std::min(nvec, per * (size_t)rank);
+        const size_t ve = std::min(nvec, vb + per);
+        seg.begin[k] = first + vb;
+        seg.end[k] = first + ve;
+        work = std::max(work, ve - vb);
+    }
+    if (work == 0) return 0;
+    size_t blocks = (work + (size_t)NVLS_THREADS * NVLS_UNROLL - 1) / ((size_t)NVLS_THREADS * NVLS_UNROLL);
+    blocks = std::max<size_t>(1, std::min<size_t>(blocks, (size_t)std::max(1, max_blocks)));
+    ++g_kernel_launches;
+    nvls_allreduce_segments_kernel<<<(unsigned)blocks, NVLS_THREADS, 0, s>>>(
+        static_cast<float*>(multicast_ptr), seg);
     return 0;
 }
 

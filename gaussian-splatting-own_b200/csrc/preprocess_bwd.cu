@@ -20,18 +20,29 @@ __device__ __forceinline__ void store3(float* p, float a, float b, float c)
     p[0] = a; p[1] = b; p[2] = c;
 }
 
+// kVecSH && !kFactor: dL_dsh rows are NOT written per thread (each row is 192 contiguous bytes,
+// so a warp's store instruction would touch 32 half sectors 192 bytes apart). Every lane leaves
+// its 16 basis values and dL/dRGB (zeros when culled) in a shared-memory tile and the warp then
+// writes its 32 x 48 block of products with fully coalesced 512-byte stores.
+constexpr int SH_TILE_STRIDE = 19;   // 16 basis values + dL/dRGB; odd => conflict-free rows
+
 // Per-Gaussian body. Returns the clamp-masked colour gradient dL/dRGB (zero for culled
 // Gaussians): dL/dsh[k] = basis_k(dir) * dL/dRGB is rank one, which the view-parallel path
 // exploits (kFactor: dL_dsh is NOT written here, the caller multicasts the returned factor).
 template <bool kVecSH, bool kFactor>
 __device__ __forceinline__ V3 preprocess_backward_body(const PreprocessBackwardParams& p, int idx,
                                                        const float* s_view, const float* s_proj,
-                                                       const float* s_cam)
+                                                       const float* s_cam, float* tile_row)
 {
+    constexpr bool kCoop = kVecSH && !kFactor;
     const size_t i = (size_t)idx;
     const int ncoef = (p.D + 1) * (p.D + 1);
 
     if (!(p.radii[idx] > 0)) {
+        if (kCoop) {
+#pragma unroll
+            for (int k = 0; k < SH_TILE_STRIDE; ++k) tile_row[k] = 0.f;
+        }
         store3(p.dL_dmean2D + 3 * i, 0.f, 0.f, 0.f);
         store3(p.dL_dcolor + 3 * i, 0.f, 0.f, 0.f);
         p.dL_dopacity[i] = 0.f;
@@ -45,7 +56,7 @@ __device__ __forceinline__ V3 preprocess_backward_body(const PreprocessBackwardP
 #pragma unroll
             for (int k = 0; k < 4; ++k) p.dL_drot[4 * i + k] = 0.f;
         }
-        if (p.M > 0 && !kFactor) {
+        if (p.M > 0 && !kFactor && !kCoop) {
             if (kVecSH) {
                 float4* dst = reinterpret_cast<float4*>(p.dL_dsh) + i * 12;
 #pragma unroll
@@ -250,6 +261,11 @@ __device__ __forceinline__ V3 preprocess_backward_body(const PreprocessBackwardP
             // (3 float4) at a time so that only 24 floats are live instead of 96
             const float4* src = reinterpret_cast<const float4*>(p.shs) + i * 12;
             float4* dst = reinterpret_cast<float4*>(p.dL_dsh) + i * 12;
+            if (kCoop) {
+#pragma unroll
+                for (int k = 0; k < 16; ++k) tile_row[k] = k < ncoef ? bas[k] : 0.f;
+                tile_row[16] = dRGB.x; tile_row[17] = dRGB.y; tile_row[18] = dRGB.z;
+            }
             // all twelve loads are issued up front (memory-level parallelism) ...
             float sh[48];
 #pragma unroll
@@ -267,7 +283,7 @@ __device__ __forceinline__ V3 preprocess_backward_body(const PreprocessBackwardP
                     const int k = 4 * c + kk;
                     const bool on = k < ncoef;
                     const float bk = on ? bas[k] : 0.f;
-                    if (!kFactor) {
+                    if (!kFactor && !kCoop) {
                         out[3 * kk] = bk * dRGB.x; out[3 * kk + 1] = bk * dRGB.y; out[3 * kk + 2] = bk * dRGB.z;
                     }
                     if (on && k > 0) {
@@ -277,7 +293,7 @@ __device__ __forceinline__ V3 preprocess_backward_body(const PreprocessBackwardP
                         dRGBdz = dRGBdz + bz[k] * s;
                     }
                 }
-                if (!kFactor) {
+                if (!kFactor && !kCoop) {
 #pragma unroll
                     for (int q = 0; q < 3; ++q)
                         dst[3 * c + q] = make_float4(out[4 * q], out[4 * q + 1], out[4 * q + 2], out[4 * q + 3]);
@@ -397,22 +413,55 @@ __global__ void __launch_bounds__(PB_THREADS) preprocess_backward_kernel(Preproc
     if (threadIdx.x < 3) s_cam[threadIdx.x] = p.cam_pos[threadIdx.x];
     __syncthreads();
 
-    const int idx = blockIdx.x * PB_THREADS + threadIdx.x;
+    constexpr bool kCoop = kVecSH && !kFactor;
+    __shared__ float s_tile[kCoop ? PB_THREADS * SH_TILE_STRIDE : 1];
+    float* tile_row = kCoop ? s_tile + threadIdx.x * SH_TILE_STRIDE : nullptr;
+
+    const int block_first = p.begin + blockIdx.x * PB_THREADS;
+    const int idx = block_first + threadIdx.x;
     V3 f = v3(0.f, 0.f, 0.f);
-    if (idx < p.P) f = preprocess_backward_body<kVecSH, kFactor>(p, idx, s_view, s_proj, s_cam);
+    if (idx < p.end)
+        f = preprocess_backward_body<kVecSH, kFactor>(p, idx, s_view, s_proj, s_cam, tile_row);
+    if (kCoop) {
+        // dL_dsh[r][k][c] = basis_k(r) * dL/dRGB_c(r): the warp's 32 rows, 384 float4, written in
+        // twelve instructions of 512 contiguous bytes each
+        __syncwarp();
+        const int lane = threadIdx.x & 31;
+        const int row0 = idx - lane;
+        const int rows = min(32, p.end - row0);
+        const float* tile = s_tile + (threadIdx.x - lane) * SH_TILE_STRIDE;
+        float4* dst = reinterpret_cast<float4*>(p.dL_dsh) + (size_t)row0 * 12;
+#pragma unroll
+        for (int j = 0; j < 12; ++j) {
+            const int q = j * 32 + lane;          // float4 index inside the warp's block
+            const int r = q / 12;
+            if (r < rows) {
+                const float* row = tile + r * SH_TILE_STRIDE;
+                const int f0 = (q - r * 12) * 4;  // first of the four floats: k = f / 3, c = f % 3
+                float o[4];
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    const int fl = f0 + t, k = fl / 3;
+                    o[t] = row[k] * row[16 + fl - 3 * k];
+                }
+                dst[q] = make_float4(o[0], o[1], o[2], o[3]);
+            }
+        }
+    }
     if (kFactor) {
         s_factor[3 * threadIdx.x] = f.x;
         s_factor[3 * threadIdx.x + 1] = f.y;
         s_factor[3 * threadIdx.x + 2] = f.z;
         __syncthreads();
-        // 3*256 floats = 192 float4; P % 4 == 0 is required by the host, so the valid part of
-        // the last block is a whole number of float4 too
-        const size_t first = (size_t)blockIdx.x * PB_THREADS * 3;            // float index in the slot
-        const size_t valid = min((size_t)PB_THREADS, (size_t)p.P - (size_t)blockIdx.x * PB_THREADS) * 3;
+        // 3*256 floats = 192 float4; begin and end are multiples of 4 (checked by the host), so
+        // the block's first float is 16-byte aligned and the valid part of the last block is a
+        // whole number of float4 too
+        const size_t first = (size_t)block_first * 3;                        // float index in the slot
+        const size_t valid = (size_t)min(PB_THREADS, p.end - block_first) * 3;
         float4* dst = reinterpret_cast<float4*>(p.factor_mc + first);
         if (threadIdx.x * 4 < valid)
             mm_st4(dst + threadIdx.x, reinterpret_cast<const float4*>(s_factor)[threadIdx.x]);
-        if (blockIdx.x == 0 && threadIdx.x < 3)
+        if (block_first == 0 && threadIdx.x < 3)
             asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(p.campos_mc + threadIdx.x),
                          "f"(s_cam[threadIdx.x])
                          : "memory");
@@ -421,55 +470,93 @@ __global__ void __launch_bounds__(PB_THREADS) preprocess_backward_kernel(Preproc
 
 // dL/dsh[i][k][c] = sum over views v of basis_k(dir_v(i)) * factor_v[i][c]   (k < (D+1)^2, else 0),
 // summed in rank order, i.e. deterministically and identically on every rank.
-__global__ void __launch_bounds__(256)
-sh_grad_from_factors_kernel(int P, int D, int M, int world, const float* __restrict__ means3D,
-                            const float* __restrict__ campos_all, const float* __restrict__ factors_all,
-                            float* __restrict__ dL_dsh)
+constexpr int SHG_THREADS = 128;   // 4 warps x 6.1 KB of transpose tile
+
+__global__ void __launch_bounds__(SHG_THREADS)
+sh_grad_from_factors_kernel(int P, int begin, int end, int D, int M, int world,
+                            const float* __restrict__ means3D, const float* __restrict__ campos_all,
+                            const float* __restrict__ factors_all, float* __restrict__ dL_dsh)
 {
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= P) return;
-    const size_t i = (size_t)idx;
+    const int idx = begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx - (int)(threadIdx.x & 31) >= end) return;          // whole warp past the range
+    const bool live = idx < end;                               // tail lanes help with the stores
+    const size_t i = (size_t)(live ? idx : end - 1);
     const int ncoef = (D + 1) * (D + 1);
     float acc[48];
 #pragma unroll
     for (int k = 0; k < 48; ++k) acc[k] = 0.f;
     const V3 mean = v3(means3D[3 * i], means3D[3 * i + 1], means3D[3 * i + 2]);
-    for (int v = 0; v < world; ++v) {
-        const float* fsrc = factors_all + ((size_t)v * P + i) * 3;
-        const V3 g = v3(fsrc[0], fsrc[1], fsrc[2]);
-        if (g.x == 0.f && g.y == 0.f && g.z == 0.f) continue;   // not seen (or fully clamped) in view v
-        const V3 cam = v3(campos_all[4 * v], campos_all[4 * v + 1], campos_all[4 * v + 2]);
-        const V3 dir_orig = mean - cam;
-        const V3 dir = dir_orig / length3(dir_orig);
-        const float x = dir.x, y = dir.y, z = dir.z;
-        const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
-        float bas[16];
-        bas[0] = kC0;
-        bas[1] = -kC1 * y; bas[2] = kC1 * z; bas[3] = -kC1 * x;
-        bas[4] = kC2_0 * xy; bas[5] = kC2_1 * yz; bas[6] = kC2_2 * (2.f * zz - xx - yy);
-        bas[7] = kC2_3 * xz; bas[8] = kC2_4 * (xx - yy);
-        bas[9] = kC3_0 * y * (3.f * xx - yy); bas[10] = kC3_1 * xy * z;
-        bas[11] = kC3_2 * y * (4.f * zz - xx - yy);
-        bas[12] = kC3_3 * z * (2.f * zz - 3.f * xx - 3.f * yy);
-        bas[13] = kC3_4 * x * (4.f * zz - xx - yy); bas[14] = kC3_5 * z * (xx - yy);
-        bas[15] = kC3_6 * x * (xx - 3.f * yy);
+    if (!live) world = 0;
+    // Views in groups of four: the group's factor loads are issued together (the loop is bound
+    // by the latency of these loads, not by the arithmetic), then consumed in view order.
+    constexpr int kGroup = 4;
+    for (int v0 = 0; v0 < world; v0 += kGroup) {
+        V3 gv[kGroup];
 #pragma unroll
-        for (int k = 0; k < 16; ++k) {
-            if (k < ncoef) {
-                // product rounded first, then added: the same value a plain sum of the per-view
-                // dL/dsh (bas*g rounded by K7) would accumulate
-                acc[3 * k] = __fadd_rn(acc[3 * k], __fmul_rn(bas[k], g.x));
-                acc[3 * k + 1] = __fadd_rn(acc[3 * k + 1], __fmul_rn(bas[k], g.y));
-                acc[3 * k + 2] = __fadd_rn(acc[3 * k + 2], __fmul_rn(bas[k], g.z));
+        for (int u = 0; u < kGroup; ++u) {
+            gv[u] = v3(0.f, 0.f, 0.f);
+            if (v0 + u < world) {
+                const float* fsrc = factors_all + ((size_t)(v0 + u) * P + i) * 3;
+                gv[u] = v3(__ldcs(fsrc), __ldcs(fsrc + 1), __ldcs(fsrc + 2));
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < kGroup; ++u) {
+            const V3 g = gv[u];
+            // not seen (or fully clamped) in this view; also skips the padding of the last group
+            if (g.x == 0.f && g.y == 0.f && g.z == 0.f) continue;
+            const int v = v0 + u;
+            const V3 cam = v3(campos_all[4 * v], campos_all[4 * v + 1], campos_all[4 * v + 2]);
+            const V3 dir_orig = mean - cam;
+            const V3 dir = dir_orig / length3(dir_orig);
+            const float x = dir.x, y = dir.y, z = dir.z;
+            const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+            float bas[16];
+            bas[0] = kC0;
+            bas[1] = -kC1 * y; bas[2] = kC1 * z; bas[3] = -kC1 * x;
+            bas[4] = kC2_0 * xy; bas[5] = kC2_1 * yz; bas[6] = kC2_2 * (2.f * zz - xx - yy);
+            bas[7] = kC2_3 * xz; bas[8] = kC2_4 * (xx - yy);
+            bas[9] = kC3_0 * y * (3.f * xx - yy); bas[10] = kC3_1 * xy * z;
+            bas[11] = kC3_2 * y * (4.f * zz - xx - yy);
+            bas[12] = kC3_3 * z * (2.f * zz - 3.f * xx - 3.f * yy);
+            bas[13] = kC3_4 * x * (4.f * zz - xx - yy); bas[14] = kC3_5 * z * (xx - yy);
+            bas[15] = kC3_6 * x * (xx - 3.f * yy);
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                if (k < ncoef) {
+                    // product rounded first, then added: the same value a plain sum of the
+                    // per-view dL/dsh (bas*g rounded by K7) would accumulate
+                    acc[3 * k] = __fadd_rn(acc[3 * k], __fmul_rn(bas[k], g.x));
+                    acc[3 * k + 1] = __fadd_rn(acc[3 * k + 1], __fmul_rn(bas[k], g.y));
+                    acc[3 * k + 2] = __fadd_rn(acc[3 * k + 2], __fmul_rn(bas[k], g.z));
+                }
             }
         }
     }
     if (M == 16 && (reinterpret_cast<uintptr_t>(dL_dsh) & 15) == 0) {
-        float4* dst = reinterpret_cast<float4*>(dL_dsh) + i * 12;
+        // A thread's row is 192 contiguous bytes; written directly, every store instruction of a
+        // warp would touch 32 half sectors 192 bytes apart. Transpose the warp's 32 x 48 tile
+        // through shared memory (row stride 49 words: conflict free) so that each instruction
+        // writes 512 contiguous bytes.
+        __shared__ float s_tile[SHG_THREADS / 32][32 * 49];
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        float* tile = s_tile[warp];
 #pragma unroll
-        for (int k = 0; k < 12; ++k)
-            dst[k] = make_float4(acc[4 * k], acc[4 * k + 1], acc[4 * k + 2], acc[4 * k + 3]);
-    } else {
+        for (int k = 0; k < 48; ++k) tile[lane * 49 + k] = acc[k];
+        __syncwarp();
+        const int row0 = idx - lane;                           // first Gaussian of this warp
+        const int rows = min(32, end - row0);
+        float4* dst = reinterpret_cast<float4*>(dL_dsh) + (size_t)row0 * 12;
+#pragma unroll
+        for (int j = 0; j < 12; ++j) {
+            const int q = j * 32 + lane;                       // float4 index inside the tile
+            const int r = q / 12, c = (q - r * 12) * 4;
+            if (r < rows) {
+                const float* src = tile + r * 49 + c;
+                __stcs(dst + q, make_float4(src[0], src[1], src[2], src[3]));
+            }
+        }
+    } else if (live) {
         float* dst = dL_dsh + i * M * 3;
 #pragma unroll
         for (int k = 0; k < 48; ++k)
@@ -480,20 +567,20 @@ sh_grad_from_factors_kernel(int P, int D, int M, int world, const float* __restr
 
 }  // namespace
 
-void launch_sh_grad_from_factors(int P, int D, int M, int world, const float* means3D,
-                                 const float* campos_all, const float* factors_all, float* dL_dsh,
-                                 cudaStream_t s)
+void launch_sh_grad_from_factors(int P, int begin, int end, int D, int M, int world,
+                                 const float* means3D, const float* campos_all,
+                                 const float* factors_all, float* dL_dsh, cudaStream_t s)
 {
-    if (P <= 0) return;
+    if (end <= begin) return;
     ++g_kernel_launches;
-    sh_grad_from_factors_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, D, M, world, means3D, campos_all,
-                                                               factors_all, dL_dsh);
+    sh_grad_from_factors_kernel<<<(end - begin + SHG_THREADS - 1) / SHG_THREADS, SHG_THREADS, 0, s>>>(
+        P, begin, end, D, M, world, means3D, campos_all, factors_all, dL_dsh);
 }
 
 void launch_preprocess_backward(const PreprocessBackwardParams& p, cudaStream_t s)
 {
-    if (p.P <= 0) return;
-    const int blocks = (p.P + PB_THREADS - 1) / PB_THREADS;
+    if (p.end <= p.begin) return;
+    const int blocks = (p.end - p.begin + PB_THREADS - 1) / PB_THREADS;
     const bool factor = p.factor_mc != nullptr && p.shs != nullptr;
     const bool vec = p.shs != nullptr && p.M == 16 &&
                      (reinterpret_cast<uintptr_t>(p.shs) & 15) == 0 &&

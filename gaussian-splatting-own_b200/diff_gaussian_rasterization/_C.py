@@ -46,7 +46,11 @@ class _BackwardArgs(C.Structure):
         ("dL_dcov3D", C.c_void_p), ("dL_dsh", C.c_void_p), ("dL_dscale", C.c_void_p),
         ("dL_drot", C.c_void_p), ("debug", C.c_int),
         ("sh_factor_multicast", C.c_void_p), ("campos_multicast", C.c_void_p),
+        ("stages", C.c_int), ("gaussian_begin", C.c_int), ("gaussian_end", C.c_int),
     ]
+
+
+BACKWARD_ACCUMULATE, BACKWARD_PREPROCESS = 1, 2
 
 
 _ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_size_t, C.c_void_p)
@@ -97,6 +101,14 @@ def lib() -> C.CDLL:
     L.bgr_sh_grad_from_factors.restype = C.c_int
     L.bgr_sh_grad_from_factors.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                            C.c_void_p, C.c_void_p, C.c_void_p]
+    L.bgr_sh_grad_from_factors_range.restype = C.c_int
+    L.bgr_sh_grad_from_factors_range.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                                 C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                 C.c_void_p]
+    L.bgr_nvls_allreduce_segments_f32.restype = C.c_int
+    L.bgr_nvls_allreduce_segments_f32.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_size_t),
+                                                  C.POINTER(C.c_size_t), C.c_int, C.c_int, C.c_int,
+                                                  C.c_void_p]
     L.bgr_nvls_visibility_or.restype = C.c_int
     L.bgr_nvls_visibility_or.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                          C.c_int, C.c_void_p]
@@ -268,12 +280,26 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
                 dL_dcolor=_ptr(dL_dcolors), dL_dopacity=_ptr(dL_dopacity),
                 dL_dmean3D=_ptr(dL_dmeans3D), dL_dcov3D=_ptr(dL_dcov3D), dL_dsh=_ptr(dL_dsh),
                 dL_dscale=_ptr(dL_dscales), dL_drot=_ptr(dL_drotations), debug=int(bool(debug)))
+            chunks = None
             if _sh_factor_hook is not None and M > 0:
                 # view-parallel path: multicast dL/dRGB instead of writing dL_dsh (see bgr.h)
                 slots = _sh_factor_hook(P, M, int(degree), means_, dL_dsh)
                 if slots is not None:
-                    a.sh_factor_multicast, a.campos_multicast = slots
-            _check(L.bgr_backward(C.byref(a), _stream(dev)))
+                    a.sh_factor_multicast, a.campos_multicast = slots[0], slots[1]
+                    chunks = slots[2] if len(slots) > 2 else None
+            if chunks is None:
+                _check(L.bgr_backward(C.byref(a), _stream(dev)))
+            else:
+                # pipelined exchange: (bounds, after_chunk) — the hook's owner exchanges the
+                # gradients of each finished Gaussian range while the next one is computed
+                bounds, after_chunk = chunks
+                a.stages = BACKWARD_ACCUMULATE
+                _check(L.bgr_backward(C.byref(a), _stream(dev)))
+                a.stages = BACKWARD_PREPROCESS
+                for p0, p1 in zip(bounds[:-1], bounds[1:]):
+                    a.gaussian_begin, a.gaussian_end = int(p0), int(p1)
+                    _check(L.bgr_backward(C.byref(a), _stream(dev)))
+                    after_chunk(int(p0), int(p1))
             # scratch may be reused by the allocator only after the kernels that read it
             scratch.record_stream(torch.cuda.current_stream(dev))
     return (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
@@ -333,6 +359,26 @@ def sh_grad_from_factors(P, D, M, world, means3D, campos_all_ptr: int, factors_a
                                               C.c_void_p(means3D.data_ptr()), C.c_void_p(campos_all_ptr),
                                               C.c_void_p(factors_all_ptr), C.c_void_p(dL_dsh.data_ptr()),
                                               _stream(device)))
+
+
+def sh_grad_from_factors_range(P, begin, end, D, M, world, means3D, campos_all_ptr: int,
+                               factors_all_ptr: int, dL_dsh, device) -> None:
+    with torch.cuda.device(device):
+        _check(lib().bgr_sh_grad_from_factors_range(
+            int(P), int(begin), int(end), int(D), int(M), int(world), C.c_void_p(means3D.data_ptr()),
+            C.c_void_p(campos_all_ptr), C.c_void_p(factors_all_ptr), C.c_void_p(dL_dsh.data_ptr()),
+            _stream(device)))
+
+
+def nvls_allreduce_segments(multicast_ptr: int, segments, rank: int, world: int, device,
+                            max_blocks: int = 296) -> None:
+    """segments: up to four (offset_floats, count_floats) pairs, all multiples of 4."""
+    n = len(segments)
+    offs = (C.c_size_t * max(n, 1))(*[int(o) for o, _ in segments])
+    cnts = (C.c_size_t * max(n, 1))(*[int(c) for _, c in segments])
+    with torch.cuda.device(device):
+        _check(lib().bgr_nvls_allreduce_segments_f32(C.c_void_p(multicast_ptr), n, offs, cnts, rank, world,
+                                                     max_blocks, _stream(device)))
 
 
 def nvls_visibility(radii, P: int, local_words_ptr: int, multicast_words_ptr: int, rank: int,

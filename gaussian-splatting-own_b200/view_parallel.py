@@ -88,7 +88,7 @@ class NvlsExchange:
     SMALL_FLOATS = 11      # ... + rotations 4: everything except sh
 
     def __init__(self, P: int, M: int, device, group: Optional[dist.ProcessGroup] = None,
-                 max_blocks: int = 296, mode: str = "factor"):
+                 max_blocks: int = 296, mode: str = "factor", chunks: int = 4):
         import torch.distributed._symmetric_memory as symm_mem
         from diff_gaussian_rasterization import _C
         self._C = _C
@@ -120,6 +120,15 @@ class NvlsExchange:
         self._have_mask = False
         self._pending = None     # (D, means3D, dL_dsh) of the backward whose factors are in flight
         self._side = None
+        # mode "factor": the backward preprocess runs in `chunks` Gaussian ranges (bounds are
+        # multiples of 1024) and each finished range is exchanged on a second stream — barrier,
+        # local dL_dsh rebuild, in-switch sum of its 11 floats/Gaussian — under the next range.
+        self.chunks = max(1, int(chunks))
+        step = max(1024, -(-(-(-P // self.chunks)) // 1024) * 1024)   # ceil(P / chunks) rounded up to 1024
+        self.bounds = list(range(0, P, step)) + [P]
+        self._piped = False
+        self.profile = False     # diagnostics: CUDA events around the pieces of all_reduce()
+        self._marks = []
         _C.set_grad_arena_provider(self._provide)
         if mode == "factor":
             _C.set_sh_factor_hook(self._factor_slots)
@@ -133,7 +142,33 @@ class NvlsExchange:
             return None
         self._pending = (degree, means3D, dL_dsh)
         mc = self.hdl.multicast_ptr
-        return (mc + 4 * (self.factors_off + self.rank * 3 * P), mc + 4 * (self.campos_off + 4 * self.rank))
+        slots = (mc + 4 * (self.factors_off + self.rank * 3 * P), mc + 4 * (self.campos_off + 4 * self.rank))
+        if self.chunks <= 1 or len(self.bounds) <= 2:
+            return slots
+        self._piped = True
+        return slots + ((self.bounds, self._after_chunk),)
+
+    def _after_chunk(self, p0: int, p1: int) -> None:
+        """Called right after the backward preprocess of Gaussians [p0, p1) was queued on the current
+        stream: exchange that range on the side stream while the next range is computed."""
+        degree, means3D, dL_dsh = self._pending
+        P, n = self.P, p1 - p0
+        cur = torch.cuda.current_stream(self.device)
+        if self._side is None:
+            self._side = torch.cuda.Stream(self.device)
+        self._side.wait_stream(cur)
+        leaf0 = P * self.NON_LEAF_FLOATS
+        base = self.buf.data_ptr()
+        with torch.cuda.stream(self._side):
+            self.hdl.barrier(channel=0)   # every rank has produced (and multicast) this range
+            self._C.sh_grad_from_factors_range(P, p0, p1, degree, self.M, self.world, means3D,
+                                               base + 4 * self.campos_off, base + 4 * self.factors_off,
+                                               dL_dsh, self.device)
+            # means3D | opacity | scales | rotations rows of the range
+            segs = [(leaf0 + 3 * p0, 3 * n), (leaf0 + 3 * P + p0, n), (leaf0 + 4 * P + 3 * p0, 3 * n),
+                    (leaf0 + 7 * P + 4 * p0, 4 * n)]
+            self._C.nvls_allreduce_segments(self.hdl.multicast_ptr, segs, self.rank, self.world,
+                                            self.device, self.max_blocks)
 
     @property
     def sparse(self):
@@ -161,7 +196,17 @@ class NvlsExchange:
         leaf0 = P * self.NON_LEAF_FLOATS
         red = lambda off, cnt: self._C.nvls_allreduce(mc, off, cnt, self.rank, self.world, self.device,  # noqa: E731
                                                       self.max_blocks)
+        if self._piped:
+            # every range was exchanged on the side stream as it was produced
+            torch.cuda.current_stream(self.device).wait_stream(self._side)
+            self._piped = False
+            self._pending = None
+            self.hdl.barrier(channel=0)    # sums broadcast everywhere; factor slots free for reuse
+            return
+        mark = self._mark
+        mark("start")
         self.hdl.barrier(channel=0)        # every rank's backward (stores, multicasts) is complete
+        mark("barrier_in")
         if self.mode == "factor" and self._pending is not None:
             degree, means3D, dL_dsh = self._pending
             base = self.buf.data_ptr()
@@ -175,7 +220,9 @@ class NvlsExchange:
                                              base + 4 * self.campos_off, base + 4 * self.factors_off,
                                              dL_dsh, self.device)
             red(leaf0, P * self.SMALL_FLOATS)
+            mark("in_switch_sum")
             cur.wait_stream(self._side)
+            mark("sh_rebuild_tail")
             self._pending = None
         elif self.mode == "rows" and self._have_mask:
             red(leaf0, P * self.DENSE_FLOATS)
@@ -188,6 +235,27 @@ class NvlsExchange:
             red(leaf0, P * self.leaf_floats)
         self._have_mask = False
         self.hdl.barrier(channel=0)        # sums broadcast everywhere; factor slots free for reuse
+        mark("barrier_out")
+
+    def _mark(self, name):
+        if self.profile:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            self._marks.append((name, e))
+
+    def profile_report(self):
+        """Mean milliseconds per piece over the profiled calls (synchronises)."""
+        torch.cuda.synchronize(self.device)
+        acc, n = {}, 0
+        prev = None
+        for name, e in self._marks:
+            if name == "start":
+                n += 1
+            else:
+                acc[name] = acc.get(name, 0.0) + prev.elapsed_time(e)
+            prev = e
+        self._marks = []
+        return {k: round(v / max(n, 1), 4) for k, v in acc.items()}
 
     def close(self):
         self._C.set_grad_arena_provider(None)

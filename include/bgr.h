@@ -113,7 +113,17 @@ typedef struct BgrBackwardArgs {
      * bgr_sh_grad_from_factors. Needs P % 4 == 0. dL_dsh is not written by bgr_backward then.   */
     float* sh_factor_multicast;  /* multicast address of slot [rank][P][3]                  */
     float* campos_multicast;     /* multicast address of slot [rank][4]                     */
+    /* Optional split of the call (0 = do everything, the drop-in behaviour). A view-parallel
+     * caller runs BGR_BACKWARD_ACCUMULATE once (clear + render backward, reference
+     * backward.cu:399-557) and then BGR_BACKWARD_PREPROCESS (backward.cu:140-396 fused) over
+     * consecutive Gaussian ranges [gaussian_begin, gaussian_end), exchanging the finished range
+     * while the next one is computed. Range bounds must be multiples of 4 on the multicast path. */
+    int    stages;
+    int    gaussian_begin;
+    int    gaussian_end;
 } BgrBackwardArgs;
+#define BGR_BACKWARD_ACCUMULATE 1
+#define BGR_BACKWARD_PREPROCESS 2
 
 /* Forward rasterization. Writes *num_rendered (total tile instances, the reference's return
  * value). geom/binning/image are grown through the callbacks exactly once each. */
@@ -172,6 +182,17 @@ BGR_API int bgr_nvls_allreduce_f32(void* multicast_ptr, size_t offset_floats, si
 BGR_API int bgr_sh_grad_from_factors(int P, int D, int M, int world, const float* means3D,
                                      const float* campos_all, const float* factors_all, float* dL_dsh,
                                      void* stream);
+/* The same for the Gaussians [begin, end) only (pipelined exchange). */
+BGR_API int bgr_sh_grad_from_factors_range(int P, int begin, int end, int D, int M, int world,
+                                           const float* means3D, const float* campos_all,
+                                           const float* factors_all, float* dL_dsh, void* stream);
+
+/* bgr_nvls_allreduce_f32 over up to four disjoint ranges in one launch (the Gaussian range
+ * [p0, p1) of the structure-of-arrays leaf block is four short ranges). Offsets and counts are in
+ * floats from multicast_ptr and must be multiples of 4. */
+BGR_API int bgr_nvls_allreduce_segments_f32(void* multicast_ptr, int nseg, const size_t* offsets_floats,
+                                            const size_t* counts_floats, int rank, int world,
+                                            int max_blocks, void* stream);
 
 /* Row-sparse variant. A Gaussian that no rank sees has an all-zero gradient row everywhere and need
  * not cross the fabric. phase 0: packs (radii > 0) into one bit per Gaussian in local_words (part of

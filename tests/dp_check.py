@@ -43,7 +43,8 @@ def main():
     torch.cuda.synchronize()
 
     mode = sys.argv[2] if len(sys.argv) > 2 else "factor"
-    ex = vp.NvlsExchange(P, 16, dev, mode=mode)
+    chunks = int(sys.argv[3]) if len(sys.argv) > 3 else 4
+    ex = vp.NvlsExchange(P, 16, dev, mode=mode, chunks=chunks)
     r = vp.ViewParallelRasterizer(exchange="nvls")
     r._nvls = ex
     peer = (rank + 1) % world
