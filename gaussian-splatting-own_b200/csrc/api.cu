@@ -277,7 +277,7 @@ BGR_API int bgr_forward(const BgrForwardArgs* a, bgr_alloc_fn geom_alloc, void* 
         int in_alt = 0;
         g_timer.begin(ST_SORT, s);
         if (radix_sort(k_in, k_alt, v_in, v_alt, (size_t)R, kf.sort_lo, kf.sort_hi,
-                       bin + BL.sort_temp, s, &in_alt) != 0)
+                       bin + BL.sort_temp, s, &in_alt, kf.tile_shift) != 0)
             return fail(BGR_ERR_INVALID_ARG, "radix sort configuration rejected");
         g_timer.end(ST_SORT, s);
         if ((rc = stage_check(debug, s, "radix sort"))) return rc;

@@ -175,7 +175,8 @@ void launch_tile_ranges(size_t R, const uint64_t* keys_sorted, const uint32_t* v
                         KeyFormat kf, uint32_t num_tiles, uint2* ranges, uint32_t* point_list,
                         cudaStream_t s);
 int  radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, size_t n,
-                int bit_lo, int bit_hi, void* temp, cudaStream_t s, int* result_in_b);
+                int bit_lo, int bit_hi, void* temp, cudaStream_t s, int* result_in_b,
+                 int scattered_from_bit = -1);
 int  radix_sort_passes(int bit_lo, int bit_hi);
 
 void launch_render_forward(int W, int H, const uint2* ranges, const uint32_t* point_list,

@@ -22,6 +22,23 @@ constexpr uint32_t ST_AGG = 1u << 30;
 constexpr uint32_t ST_PREFIX = 2u << 30;
 constexpr uint32_t ST_VALUE_MASK = (1u << 30) - 1u;
 
+// Lanes holding my digit. kBallot: eight ballots (constant cost); otherwise MATCH.ANY, whose cost
+// grows with the number of distinct digits in the warp (cheap on the depth digits, where the
+// ~4 keys of one Gaussian are adjacent and equal; 4-5x slower on the tile digits).
+template <bool kBallot>
+__device__ __forceinline__ unsigned digit_peers(uint32_t d, bool valid)
+{
+    if (!kBallot) return __match_any_sync(0xffffffffu, d);
+    unsigned peers = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+    for (int b = 0; b < RADIX_BITS; ++b) {
+        const bool bit = (d >> b) & 1u;
+        const unsigned m = __ballot_sync(0xffffffffu, bit);
+        peers &= bit ? m : ~m;
+    }
+    return valid ? peers : (1u << (threadIdx.x & 31));
+}
+
 __global__ void __launch_bounds__(256)
 sort_hist_kernel(const uint64_t* __restrict__ keys, uint32_t n, int bit_lo, int bit_hi, int npasses,
                  uint32_t* __restrict__ hist)
@@ -39,8 +56,7 @@ sort_hist_kernel(const uint64_t* __restrict__ keys, uint32_t n, int bit_lo, int 
             const int shift = bit_lo + p * RADIX_BITS;
             const int nb = min(RADIX_BITS, bit_hi - shift);
             const uint32_t d = valid ? ((uint32_t)(key >> shift) & ((1u << nb) - 1u)) : 0xffffffffu;
-            const unsigned peers = __match_any_sync(0xffffffffu, d);
-            if (valid && lane == __ffs(peers) - 1) atomicAdd(&s_hist[p * RADIX + d], __popc(peers));
+            if (valid) atomicAdd(&s_hist[p * RADIX + d], 1u);
         }
     }
     __syncthreads();
@@ -70,7 +86,7 @@ __global__ void __launch_bounds__(RADIX) sort_bases_kernel(uint32_t* __restrict_
     h[t] = off + incl - c;
 }
 
-template <bool PAIRS>
+template <bool PAIRS, bool kBallot>
 __global__ void __launch_bounds__(SORT_THREADS)
 onesweep_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ keys_out,
                 const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out, uint32_t n,
@@ -110,7 +126,7 @@ onesweep_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ key
     for (int i = 0; i < SORT_ITEMS; ++i) {
         const bool valid = (warp_base + i * 32) < valid_count;
         const uint32_t d = valid ? ((uint32_t)(key[i] >> shift) & digit_mask) : 0xffffffffu;
-        const unsigned peers = __match_any_sync(0xffffffffu, d);
+        const unsigned peers = digit_peers<kBallot>(d, valid);
         const int leader = __ffs(peers) - 1;
         uint32_t old = 0;
         if (valid && lane == leader) {
@@ -205,7 +221,8 @@ int radix_sort_passes(int bit_lo, int bit_hi)
 }
 
 int radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, size_t n,
-               int bit_lo, int bit_hi, void* temp, cudaStream_t s, int* result_in_b)
+               int bit_lo, int bit_hi, void* temp, cudaStream_t s, int* result_in_b,
+               int scattered_from_bit)
 {
     static_assert(SORT_THREADS == RADIX, "one thread per digit in the look-back stage");
     *result_in_b = 0;
@@ -223,9 +240,13 @@ int radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* v
 
     static bool attr_done = false;
     if (!attr_done) {
-        cudaFuncSetAttribute(onesweep_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaFuncSetAttribute(onesweep_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)onesweep_smem(false));
-        cudaFuncSetAttribute(onesweep_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaFuncSetAttribute(onesweep_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)onesweep_smem(false));
+        cudaFuncSetAttribute(onesweep_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)onesweep_smem(true));
+        cudaFuncSetAttribute(onesweep_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)onesweep_smem(true));
         attr_done = true;
     }
@@ -246,13 +267,23 @@ int radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* v
         const uint32_t mask = (1u << nb) - 1u;
         uint32_t* st = status + (size_t)p * L.nblocks * RADIX;
         ++g_kernel_launches;
-        if (pairs)
-            onesweep_kernel<true><<<(unsigned)L.nblocks, SORT_THREADS, onesweep_smem(true), s>>>(
-                kin, kout, vin, vout, (uint32_t)n, shift, mask, hist + p * RADIX, st, tickets + p);
+        // digits that reach into [scattered_from_bit, ...) are high-entropy inside a warp
+        const bool ballot = scattered_from_bit >= 0 && shift + nb > scattered_from_bit;
+        const unsigned nblk = (unsigned)L.nblocks;
+        const size_t smem = onesweep_smem(pairs);
+        const uint32_t* bases = hist + p * RADIX;
+        if (pairs && ballot)
+            onesweep_kernel<true, true><<<nblk, SORT_THREADS, smem, s>>>(
+                kin, kout, vin, vout, (uint32_t)n, shift, mask, bases, st, tickets + p);
+        else if (pairs)
+            onesweep_kernel<true, false><<<nblk, SORT_THREADS, smem, s>>>(
+                kin, kout, vin, vout, (uint32_t)n, shift, mask, bases, st, tickets + p);
+        else if (ballot)
+            onesweep_kernel<false, true><<<nblk, SORT_THREADS, smem, s>>>(
+                kin, kout, nullptr, nullptr, (uint32_t)n, shift, mask, bases, st, tickets + p);
         else
-            onesweep_kernel<false><<<(unsigned)L.nblocks, SORT_THREADS, onesweep_smem(false), s>>>(
-                kin, kout, nullptr, nullptr, (uint32_t)n, shift, mask, hist + p * RADIX, st,
-                tickets + p);
+            onesweep_kernel<false, false><<<nblk, SORT_THREADS, smem, s>>>(
+                kin, kout, nullptr, nullptr, (uint32_t)n, shift, mask, bases, st, tickets + p);
         std::swap(kin, kout);
         std::swap(vin, vout);
     }
