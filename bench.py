@@ -54,10 +54,11 @@ def parse_args():
     ap.add_argument("--res", choices=("800x800", "1080p", "4k"), default="1080p")
     ap.add_argument("--skip-cpu-baseline", action="store_true")
     ap.add_argument("--skip-e2e", action="store_true")
-    ap.add_argument("--chunks", type=int, default=1,
+    ap.add_argument("--chunks", type=int, default=2,
                     help="N > 1, --exchange nvls: Gaussian ranges the backward preprocess is pipelined "
                          "against the exchange in (1 = exchange after the backward)")
-    ap.add_argument("--nvls-blocks", type=int, default=296, help="CTAs of the in-switch sum kernel")
+    ap.add_argument("--nvls-blocks", type=int, default=0,
+                    help="CTAs of the in-switch sum kernel (0 = the exchange mode's default)")
     ap.add_argument("--exchange", choices=("nvls", "nvls-rows", "nvls-dense", "nccl"), default="nvls",
                     help="N > 1, ours: in-switch multimem kernel of libbgr (default) or ncclAllReduce")
     return ap.parse_args()
@@ -162,7 +163,7 @@ class Workload:
                 binning, img, False)
 
 
-def make_native_step(backend, wl, world, impl, exchange="nccl", chunks=1, nvls_blocks=296):
+def make_native_step(backend, wl, world, impl, exchange="nccl", chunks=2, nvls_blocks=0):
     """forward + backward through the backend's `_C`-signature calls; N > 1 adds the all-reduce."""
     import torch.distributed as dist
     import view_parallel as vp
@@ -170,7 +171,7 @@ def make_native_step(backend, wl, world, impl, exchange="nccl", chunks=1, nvls_b
     if world > 1 and impl == "ours" and exchange.startswith("nvls"):
         nvls = vp.NvlsExchange(wl.P, 16, wl.device,
                                mode={"nvls": "factor", "nvls-rows": "rows", "nvls-dense": "dense"}[exchange],
-                               chunks=chunks, max_blocks=nvls_blocks)
+                               chunks=chunks, max_blocks=nvls_blocks or None)
     make_native_step.nvls = nvls
 
     def step():

@@ -88,14 +88,14 @@ class NvlsExchange:
     SMALL_FLOATS = 11      # ... + rotations 4: everything except sh
 
     def __init__(self, P: int, M: int, device, group: Optional[dist.ProcessGroup] = None,
-                 max_blocks: int = 296, mode: str = "factor", chunks: int = 4):
+                 max_blocks: Optional[int] = None, mode: str = "factor", chunks: int = 2):
         import torch.distributed._symmetric_memory as symm_mem
         from diff_gaussian_rasterization import _C
         self._C = _C
         self.P, self.M, self.device = P, M, torch.device(device)
         self.leaf_floats = self.SMALL_FLOATS + 3 * M
         self.numel = P * (self.NON_LEAF_FLOATS + self.leaf_floats)
-        self.max_blocks = max_blocks
+        self._max_blocks_arg = max_blocks
         grp = group if group is not None else dist.group.WORLD
         world = dist.get_world_size(grp)
         up4 = lambda n: (n + 3) // 4 * 4  # noqa: E731
@@ -111,6 +111,12 @@ class NvlsExchange:
         if mode not in ("factor", "rows", "dense"):
             raise ValueError("mode must be 'factor', 'rows' or 'dense'")
         self.mode = mode
+        # CTAs of the in-switch sum. Mode "factor" runs it BESIDE the HBM-bound dL_dsh rebuild and
+        # the next range's preprocess: its multimem requests are slow (fabric round trips) and, with
+        # a CTA on every SM, starve the other kernels' loads (measured: rebuild 0.14 -> 0.48 ms).
+        # 32 CTAs keep the fabric as busy and leave 116 SMs alone. Alone (rows / dense) it gets 296.
+        self.max_blocks = self._max_blocks_arg if self._max_blocks_arg is not None else \
+            (32 if mode == "factor" else 296)
         total = self.factors_off + (world * P * 3 if mode == "factor" else 0)
         self.buf = symm_mem.empty(total, dtype=torch.float32, device=self.device)
         self.hdl = symm_mem.rendezvous(self.buf, grp)
@@ -119,7 +125,7 @@ class NvlsExchange:
         self.rank, self.world = self.hdl.rank, self.hdl.world_size
         self._have_mask = False
         self._pending = None     # (D, means3D, dL_dsh) of the backward whose factors are in flight
-        self._side = None
+        self._side = self._side2 = None
         # mode "factor": the backward preprocess runs in `chunks` Gaussian ranges (bounds are
         # multiples of 1024) and each finished range is exchanged on a second stream — barrier,
         # local dL_dsh rebuild, in-switch sum of its 11 floats/Gaussian — under the next range.
@@ -129,6 +135,7 @@ class NvlsExchange:
         self._piped = False
         self.profile = False     # diagnostics: CUDA events around the pieces of all_reduce()
         self._marks = []
+        self._side_marks = []
         _C.set_grad_arena_provider(self._provide)
         if mode == "factor":
             _C.set_sh_factor_hook(self._factor_slots)
@@ -154,21 +161,30 @@ class NvlsExchange:
         degree, means3D, dL_dsh = self._pending
         P, n = self.P, p1 - p0
         cur = torch.cuda.current_stream(self.device)
-        if self._side is None:
-            self._side = torch.cuda.Stream(self.device)
+        self._make_streams()
         self._side.wait_stream(cur)
         leaf0 = P * self.NON_LEAF_FLOATS
         base = self.buf.data_ptr()
         with torch.cuda.stream(self._side):
             self.hdl.barrier(channel=0)   # every rank has produced (and multicast) this range
+            ready = torch.cuda.Event()
+            ready.record()
+            # the fabric-bound kernel first (one CTA per SM, high-priority stream): the HBM-bound
+            # rebuild and the next range's preprocess fill the rest of the machine around it
+            segs = [(leaf0 + 3 * p0, 3 * n), (leaf0 + 3 * P + p0, n), (leaf0 + 4 * P + 3 * p0, 3 * n),
+                    (leaf0 + 7 * P + 4 * p0, 4 * n)]   # means3D | opacity | scales | rotations rows
+            self._C.nvls_allreduce_segments(self.hdl.multicast_ptr, segs, self.rank, self.world,
+                                            self.device, self.max_blocks)
+        self._side2.wait_event(ready)
+        with torch.cuda.stream(self._side2):
             self._C.sh_grad_from_factors_range(P, p0, p1, degree, self.M, self.world, means3D,
                                                base + 4 * self.campos_off, base + 4 * self.factors_off,
                                                dL_dsh, self.device)
-            # means3D | opacity | scales | rotations rows of the range
-            segs = [(leaf0 + 3 * p0, 3 * n), (leaf0 + 3 * P + p0, n), (leaf0 + 4 * P + 3 * p0, 3 * n),
-                    (leaf0 + 7 * P + 4 * p0, 4 * n)]
-            self._C.nvls_allreduce_segments(self.hdl.multicast_ptr, segs, self.rank, self.world,
-                                            self.device, self.max_blocks)
+
+    def _make_streams(self):
+        if self._side is None:
+            self._side = torch.cuda.Stream(self.device, priority=-1)   # in-switch sums
+            self._side2 = torch.cuda.Stream(self.device)                # local dL_dsh rebuild
 
     @property
     def sparse(self):
@@ -198,7 +214,9 @@ class NvlsExchange:
                                                       self.max_blocks)
         if self._piped:
             # every range was exchanged on the side stream as it was produced
-            torch.cuda.current_stream(self.device).wait_stream(self._side)
+            cur = torch.cuda.current_stream(self.device)
+            cur.wait_stream(self._side)
+            cur.wait_stream(self._side2)
             self._piped = False
             self._pending = None
             self.hdl.barrier(channel=0)    # sums broadcast everywhere; factor slots free for reuse
@@ -210,18 +228,30 @@ class NvlsExchange:
         if self.mode == "factor" and self._pending is not None:
             degree, means3D, dL_dsh = self._pending
             base = self.buf.data_ptr()
-            # the local rebuild of dL_dsh (HBM-bound) runs beside the in-switch sum (NVLink-bound)
+            # The local rebuild of dL_dsh (HBM-bound) runs beside the in-switch sum (NVLink-bound).
+            # The sum is launched FIRST: its one CTA per SM is resident at once and the rebuild's
+            # 23k CTAs fill in around it; the other way round the block scheduler hands out the
+            # rebuild's CTAs first and the two kernels run back to back (measured).
             cur = torch.cuda.current_stream(self.device)
-            if self._side is None:
-                self._side = torch.cuda.Stream(self.device)
-            self._side.wait_stream(cur)
-            with torch.cuda.stream(self._side):
+            self._make_streams()
+            ready = torch.cuda.Event()
+            ready.record()
+            red(leaf0, P * self.SMALL_FLOATS)
+            self._side2.wait_event(ready)
+            with torch.cuda.stream(self._side2):
+                rb0 = rb1 = None
+                if self.profile:
+                    rb0 = torch.cuda.Event(enable_timing=True)
+                    rb0.record()
                 self._C.sh_grad_from_factors(P, degree, self.M, self.world, means3D,
                                              base + 4 * self.campos_off, base + 4 * self.factors_off,
                                              dL_dsh, self.device)
-            red(leaf0, P * self.SMALL_FLOATS)
+                if self.profile:
+                    rb1 = torch.cuda.Event(enable_timing=True)
+                    rb1.record()
+                    self._side_marks.append((self._marks[-1][1], rb0, rb1))
             mark("in_switch_sum")
-            cur.wait_stream(self._side)
+            cur.wait_stream(self._side2)
             mark("sh_rebuild_tail")
             self._pending = None
         elif self.mode == "rows" and self._have_mask:
@@ -255,7 +285,13 @@ class NvlsExchange:
                 acc[name] = acc.get(name, 0.0) + prev.elapsed_time(e)
             prev = e
         self._marks = []
-        return {k: round(v / max(n, 1), 4) for k, v in acc.items()}
+        out = {k: round(v / max(n, 1), 4) for k, v in acc.items()}
+        if self._side_marks:   # the rebuild on its own stream, relative to the end of barrier_in
+            m = len(self._side_marks)
+            out["rebuild_start_after_barrier"] = round(sum(b.elapsed_time(r0) for b, r0, _ in self._side_marks) / m, 4)
+            out["rebuild_duration"] = round(sum(r0.elapsed_time(r1) for _, r0, r1 in self._side_marks) / m, 4)
+            self._side_marks = []
+        return out
 
     def close(self):
         self._C.set_grad_arena_provider(None)

@@ -43,7 +43,7 @@ def main():
     torch.cuda.synchronize()
 
     mode = sys.argv[2] if len(sys.argv) > 2 else "factor"
-    chunks = int(sys.argv[3]) if len(sys.argv) > 3 else 4
+    chunks = int(sys.argv[3]) if len(sys.argv) > 3 else 2
     ex = vp.NvlsExchange(P, 16, dev, mode=mode, chunks=chunks)
     r = vp.ViewParallelRasterizer(exchange="nvls")
     r._nvls = ex
@@ -63,7 +63,7 @@ def main():
                 # two executions of the backward differ at the atomics' rounding level, so this is
                 # a tolerance comparison; the exactness claim is "identical across ranks".
                 err = (got.double() - exp.double()).abs()
-                tol = 1e-4 * exp.abs().max().item() + 1e-3 * exp.double().abs()
+                tol = 5e-4 * exp.abs().max().item() + 1e-3 * exp.double().abs()   # atomics-order noise of two runs
                 bad = int((err > tol).sum())
                 ok = ok and bad == 0
                 print(f"[rank {rank} {time.time() - t0:5.1f}s] sparse={sparse} it={it} {name}: max err "
