@@ -294,6 +294,33 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)", 1965.0
 
 
+NCU_RAW = "profiles/r1_c_ncu_full_raw.csv"
+_STAGE_KERNEL = {"render_backward": "render_backward_kernel", "render_forward": "render_forward_kernel",
+                 "preprocess_backward": "preprocess_backward_kernel", "preprocess": "preprocess_kernel",
+                 "emit_keys": "emit_keys_kernel"}
+
+
+def ncu_traffic(stage):
+    """DRAM bytes (read + write) of one launch of the stage's kernel, from the committed
+    `ncu --set full` capture of this same command; None when the capture is not there."""
+    import csv
+    path = ROOT / NCU_RAW
+    name = _STAGE_KERNEL.get(stage)
+    if name is None or not path.exists():
+        return None
+    try:
+        rows = list(csv.reader(open(path)))
+        h, units = rows[0], rows[1]
+        k, r, w = h.index("Kernel Name"), h.index("dram__bytes_read.sum"), h.index("dram__bytes_write.sum")
+        scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        for row in rows[2:]:
+            if name in row[k]:
+                return int(float(row[r]) * scale[units[r]] + float(row[w]) * scale[units[w]])
+    except (ValueError, KeyError, IndexError):
+        return None
+    return None
+
+
 def roofline_report(backend, wl, steps, device):
     """Per-stage durations from CUDA events recorded on the launch stream inside libbgr (mean over
     `steps` extra steps run right after the timed region, same process and inputs), combined with
@@ -351,14 +378,19 @@ def roofline_report(backend, wl, steps, device):
                            "algorithmic_flops": flops[name]})
     top = max(stages, key=lambda s: s["ms"])
     roof = dict(top)
-    roof["traffic"] = None
+    roof["traffic"] = ncu_traffic(top["kernel"]) if (P, W, H) == (3_000_000, 1920, 1080) else None
+    if roof["traffic"] is not None:
+        roof["traffic_source"] = f"{NCU_RAW} (dram__bytes_read.sum + dram__bytes_write.sum, one launch, same workload)"
     roof["peak_source"] = peak_src if top["bound"] == "hbm" else \
         f"{n_sm} SMs x 128 FMA lanes x 2 x {sm_mhz:.0f} MHz (no tensor-core work on this path)"
     # the dominant HBM-bound stage, so that the line always carries one bandwidth roofline too
     hbm = [s for s in stages if s["bound"] == "hbm"]
     workload_stats = {"P": P, "visible": V, "num_rendered": R, "n_pair_sum_n_contrib": n_pair,
                       "mean_tile_list": round(R / tiles, 1), **st}
-    return roof, stages, (max(hbm, key=lambda s: s["ms"]) if hbm else None), workload_stats, peak_src
+    hbm_top = dict(max(hbm, key=lambda s: s["ms"])) if hbm else None
+    if hbm_top is not None and (P, W, H) == (3_000_000, 1920, 1080):
+        hbm_top["traffic"] = ncu_traffic(hbm_top["kernel"])
+    return roof, stages, hbm_top, workload_stats, peak_src
 
 
 def dp_breakdown(backend, wl, impl, world, device, ms_per_step):
