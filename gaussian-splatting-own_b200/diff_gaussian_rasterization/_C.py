@@ -280,7 +280,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
                 dL_dcolor=_ptr(dL_dcolors), dL_dopacity=_ptr(dL_dopacity),
                 dL_dmean3D=_ptr(dL_dmeans3D), dL_dcov3D=_ptr(dL_dcov3D), dL_dsh=_ptr(dL_dsh),
                 dL_dscale=_ptr(dL_dscales), dL_drot=_ptr(dL_drotations), debug=int(bool(debug)))
-            chunks = None
+            chunks = (_backward_ranges, lambda p0, p1: None) if _backward_ranges else None
             if _sh_factor_hook is not None and M > 0:
                 # view-parallel path: multicast dL/dRGB instead of writing dL_dsh (see bgr.h)
                 slots = _sh_factor_hook(P, M, int(degree), means_, dL_dsh)
@@ -342,6 +342,15 @@ def nvls_allreduce(multicast_ptr: int, offset_floats: int, count_floats: int, ra
 
 
 _sh_factor_hook = None
+_backward_ranges = None
+
+
+def set_backward_ranges(bounds) -> None:
+    """bounds = [0, ..., P] (or None): run the backward as ACCUMULATE + one PREPROCESS call per
+    Gaussian range (BgrBackwardArgs.stages). Results are identical to the single call; the
+    view-parallel exchange uses the same split to overlap communication (view_parallel.py)."""
+    global _backward_ranges
+    _backward_ranges = list(bounds) if bounds else None
 
 
 def set_sh_factor_hook(fn) -> None:

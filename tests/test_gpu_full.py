@@ -276,3 +276,64 @@ def test_non_default_stream_and_second_device_context(C_):
         _, o = util.native_forward(C_, sc, cam, bg)
     s.synchronize()
     assert torch.equal(o[1], base[1])
+
+
+def test_staged_backward_matches_single_call(C_):
+    """BgrBackwardArgs.stages: ACCUMULATE once + PREPROCESS over Gaussian ranges must give what the
+    single call gives (two executions differ only by the atomics' summation order)."""
+    P = 50_001          # ragged: the last range is 1 Gaussian, bounds are not multiples of 4
+    scene, cam = make_case(P, "800x800", view_seed=2)
+    args, out = util.native_forward(C_, scene, cam, torch.zeros(3), 3, 1.0)
+    dpix = synthetic.make_upstream_grad(cam.image_height, cam.image_width, seed=5)
+    whole = [g.clone() for g in util.native_backward(C_, args, out, dpix)]
+    C_.set_backward_ranges([0, 1, 4097, 20_000, 50_000, P])
+    try:
+        staged = util.native_backward(C_, args, out, dpix)
+    finally:
+        C_.set_backward_ranges(None)
+    for name, a, b in zip(GRAD_NAMES, staged, whole):
+        ok, msg = grad_close(a.cpu().numpy(), b.cpu().numpy(), scale=1e3)
+        assert ok, f"{name}: {msg}"
+    # rows of culled Gaussians are exact zeros in both
+    culled = out[2] <= 0
+    assert float(staged[3][culled].abs().max()) == 0.0 and float(staged[5][culled].abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("world,degree", [(1, 3), (3, 2), (8, 3)])
+def test_sh_gradient_rebuild_from_factors(C_, world, degree):
+    """View-parallel path, single-GPU part: dL_dsh = sum_v basis(dir_v) x dL/dRGB_v from `world`
+    factor slots (local memory stands in for the multicast buffer) against an fp64 restatement of
+    the reference's per-view SH backward (backward.cu:21-137), full range and a sub-range."""
+    P = 70_003
+    g = torch.Generator().manual_seed(world * 10 + degree)
+    means = (torch.rand(P, 3, generator=g) * 10 - 5).cuda()
+    campos = torch.zeros(world, 4)
+    campos[:, :3] = torch.randn(world, 3, generator=g) * 8
+    factors = torch.randn(world, P, 3, generator=g) * (torch.rand(world, P, 1, generator=g) < 0.4)
+    campos, factors = campos.cuda(), factors.cuda()
+    C0, C1 = 0.28209479177387814, 0.4886025119029199
+    C2 = [1.0925484305920792, -1.0925484305920792, 0.31539156525252005, -1.0925484305920792, 0.5462742152960396]
+    C3 = [-0.5900435899266435, 2.890611442640554, -0.4570457994644658, 0.3731763325901154,
+          -0.4570457994644658, 1.445305721320277, -0.5900435899266435]
+    want = torch.zeros(P, 16, 3, dtype=torch.float64, device="cuda")
+    for v in range(world):
+        d = means.double() - campos[v, :3].double()
+        d = d / d.norm(dim=1, keepdim=True)
+        x, y, z = d[:, 0], d[:, 1], d[:, 2]
+        xx, yy, zz, xy, yz, xz = x * x, y * y, z * z, x * y, y * z, x * z
+        b = [torch.full_like(x, C0), -C1 * y, C1 * z, -C1 * x, C2[0] * xy, C2[1] * yz,
+             C2[2] * (2 * zz - xx - yy), C2[3] * xz, C2[4] * (xx - yy), C3[0] * y * (3 * xx - yy),
+             C3[1] * xy * z, C3[2] * y * (4 * zz - xx - yy), C3[3] * z * (2 * zz - 3 * xx - 3 * yy),
+             C3[4] * x * (4 * zz - xx - yy), C3[5] * z * (xx - yy), C3[6] * x * (xx - 3 * yy)]
+        B = torch.stack(b, 1)[:, :(degree + 1) ** 2]
+        want[:, :B.shape[1]] += B[:, :, None] * factors[v].double()[:, None, :]
+    dsh = torch.full((P, 16, 3), float("nan"), device="cuda")
+    C_.sh_grad_from_factors(P, degree, 16, world, means, campos.data_ptr(), factors.data_ptr(), dsh, "cuda")
+    assert (dsh.double() - want).abs().max().item() < 1e-5      # fp32 products and sums, |x| <~ 10
+    assert float(dsh[:, (degree + 1) ** 2:].abs().max()) == 0.0 if degree < 3 else True
+    # sub-range: rows outside [begin, end) are left alone, rows inside are identical to the full call
+    part = torch.full((P, 16, 3), 7.0, device="cuda")
+    C_.sh_grad_from_factors_range(P, 1025, P - 30, degree, 16, world, means, campos.data_ptr(),
+                                  factors.data_ptr(), part, "cuda")
+    assert float(part[:1025].min()) == 7.0 and float(part[P - 30:].min()) == 7.0 and float(part[P - 30:].max()) == 7.0
+    assert torch.equal(part[1025:P - 30], dsh[1025:P - 30])
