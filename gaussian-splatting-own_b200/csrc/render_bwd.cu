@@ -10,7 +10,7 @@
 //  * same record gather + conservative tile rejection + ordered compaction as the forward;
 //  * the inner loop is warp-uniform: a splat that no lane of the warp blends is skipped by one
 //    vote; otherwise the nine per-pixel gradient terms are reduced across the warp with a
-//    transposing butterfly (14 shuffles instead of 45) and leave the SM as ONE reduction per
+//    transposing butterfly (12 shuffles instead of 45) and leave the SM as ONE reduction per
 //    component per (warp, splat) instead of one per (pixel, splat): 9 REDs instead of up to 288;
 //  * the accumulators live in one 48-byte AoS row per Gaussian (bgr_common.cuh ACC_STRIDE) that the
 //    fused backward preprocess consumes directly.
@@ -207,22 +207,22 @@ render_backward_kernel(int W, int H, const uint2* __restrict__ ranges,
             float u1 = (h2 ? w3 : w1) + __shfl_xor_sync(0xffffffffu, h2 ? w1 : w3, 8);
             const bool h3 = (lane & 4) != 0;
             float sacc = (h3 ? u1 : u0) + __shfl_xor_sync(0xffffffffu, h3 ? u0 : u1, 4);
-            sacc += __shfl_xor_sync(0xffffffffu, sacc, 2);
-            sacc += __shfl_xor_sync(0xffffffffu, sacc, 1);
-            // ninth value: plain butterfly
+            // ninth value: plain butterfly over lane bits 4..2, then it shares the last two
+            // steps with the other eight (lanes with bit 1 set carry it from here on)
             v8 += __shfl_xor_sync(0xffffffffu, v8, 16);
             v8 += __shfl_xor_sync(0xffffffffu, v8, 8);
             v8 += __shfl_xor_sync(0xffffffffu, v8, 4);
-            v8 += __shfl_xor_sync(0xffffffffu, v8, 2);
-            v8 += __shfl_xor_sync(0xffffffffu, v8, 1);
+            const bool h4 = (lane & 2) != 0;
+            float fin = (h4 ? v8 : sacc) + __shfl_xor_sync(0xffffffffu, h4 ? sacc : v8, 2);
+            fin += __shfl_xor_sync(0xffffffffu, fin, 1);
 
             float* row = acc + (size_t)__float_as_uint(c.w) * ACC_STRIDE;
-            // lane 4k holds value index k = bit2 + 2*bit3 + 4*bit4 of the lane id
+            // lane 4k holds value index k = bit2 + 2*bit3 + 4*bit4 of the lane id; lane 2 the ninth
             if ((lane & 3) == 0) {
                 const int vi = ((lane >> 2) & 1) | (((lane >> 3) & 1) << 1) | (((lane >> 4) & 1) << 2);
-                atomicAdd(row + vi, sacc);
-            } else if (lane == 1) {
-                atomicAdd(row + 8, v8);
+                atomicAdd(row + vi, fin);
+            } else if (lane == 2) {
+                atomicAdd(row + 8, fin);
             }
         }
         }
