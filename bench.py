@@ -168,10 +168,24 @@ def make_native_step(backend, wl, world, impl, exchange="nccl", chunks=2, nvls_b
     import torch.distributed as dist
     import view_parallel as vp
     nvls = None
+    make_native_step.fallback = None
     if world > 1 and impl == "ours" and exchange.startswith("nvls"):
-        nvls = vp.NvlsExchange(wl.P, 16, wl.device,
-                               mode={"nvls": "factor", "nvls-rows": "rows", "nvls-dense": "dense"}[exchange],
-                               chunks=chunks, max_blocks=nvls_blocks or None)
+        try:
+            nvls = vp.NvlsExchange(wl.P, 16, wl.device,
+                                   mode={"nvls": "factor", "nvls-rows": "rows", "nvls-dense": "dense"}[exchange],
+                                   chunks=chunks, max_blocks=nvls_blocks or None)
+            ok = torch.ones(1, device=wl.device)
+        except Exception as e:  # no NVLink multicast / symmetric memory on this box
+            make_native_step.fallback = f"{type(e).__name__}: {e}"[:200]
+            ok = torch.zeros(1, device=wl.device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)      # every rank takes the same path
+        if float(ok) == 0.0:
+            if nvls is not None:
+                nvls.close()
+            nvls = None
+            make_native_step.fallback = make_native_step.fallback or "a peer rank could not set up NVLS"
+            print(f"[bench] NVLS exchange unavailable ({make_native_step.fallback}); "
+                  "using the NCCL all-reduce of the gradient arena", file=sys.stderr)
     make_native_step.nvls = nvls
 
     def step():
@@ -518,6 +532,8 @@ def main():
         line["cpu_baseline"] = {"value": line["value"], "unit": "views/s", "cores": 0, "kind": "reference",
                                 "sample": "not a CPU run: reference CUDA extension, same workload and harness"}
     if world > 1:
+        if getattr(make_native_step, "fallback", None):
+            line["config"]["parallelism"] += f" [fell back to nccl: {make_native_step.fallback}]"
         nvls = getattr(make_native_step, "nvls", None)
         pieces = None
         if nvls is not None:      # exchange pieces, outside the timed region
