@@ -46,7 +46,7 @@ constexpr int PRE_THREADS = 256;
 // kVecSH: shs has M == 16 coefficients and a 16-byte aligned base, so a Gaussian's 48 floats are
 // fetched as twelve 128-bit loads.
 template <bool kVecSH>
-__global__ void __launch_bounds__(PRE_THREADS) preprocess_kernel(PreprocessParams p)
+__global__ void __launch_bounds__(PRE_THREADS, 4) preprocess_kernel(PreprocessParams p)
 {
     __shared__ float s_view[16], s_proj[16], s_cam[3];
     if (threadIdx.x < 16) {

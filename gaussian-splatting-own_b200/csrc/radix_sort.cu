@@ -87,7 +87,7 @@ __global__ void __launch_bounds__(RADIX) sort_bases_kernel(uint32_t* __restrict_
 }
 
 template <bool PAIRS, bool kBallot>
-__global__ void __launch_bounds__(SORT_THREADS)
+__global__ void __launch_bounds__(SORT_THREADS, 4)
 onesweep_kernel(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ keys_out,
                 const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out, uint32_t n,
                 int shift, uint32_t digit_mask, const uint32_t* __restrict__ bases,

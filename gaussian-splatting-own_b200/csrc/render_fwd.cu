@@ -27,7 +27,7 @@ namespace {
 //   stats[1] (pixel, splat) pairs examined (power evaluated),
 //   stats[2] pairs whose expf was evaluated,  stats[3] pairs blended into the pixel.
 template <bool kStats>
-__global__ void __launch_bounds__(RENDER_THREADS)
+__global__ void __launch_bounds__(RENDER_THREADS, 5)
 render_forward_kernel(int W, int H, const uint2* __restrict__ ranges,
                       const uint32_t* __restrict__ point_list, const GaussRec* __restrict__ rec,
                       const float* __restrict__ bg, float* __restrict__ final_T,
