@@ -11,6 +11,7 @@
 //      memory so that global writes are contiguous runs per digit.
 // Stability: keys are taken in memory order warp by warp (warp-striped), ranks inside a warp step
 // follow lane order, steps follow item order, warps follow warp order, blocks follow block order.
+#include <atomic>
 #include "bgr_common.cuh"
 
 namespace bgr {
@@ -238,8 +239,12 @@ int radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* v
     uint32_t* status = reinterpret_cast<uint32_t*>(tb + L.status);
     cudaMemsetAsync(tb, 0, L.status + (size_t)npasses * L.nblocks * RADIX * 4, s);
 
-    static bool attr_done = false;
-    if (!attr_done) {
+    // function attributes are per device (context): opt in once on each device that sorts
+    static std::atomic<unsigned long long> attr_done_mask{0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const unsigned long long dev_bit = 1ull << (dev & 63);
+    if ((attr_done_mask.load(std::memory_order_relaxed) & dev_bit) == 0) {
         cudaFuncSetAttribute(onesweep_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)onesweep_smem(false));
         cudaFuncSetAttribute(onesweep_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -248,7 +253,7 @@ int radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* v
                              (int)onesweep_smem(true));
         cudaFuncSetAttribute(onesweep_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)onesweep_smem(true));
-        attr_done = true;
+        attr_done_mask.fetch_or(dev_bit, std::memory_order_relaxed);
     }
 
     const unsigned hist_blocks = (unsigned)std::min<size_t>((n + 255) / 256, 148 * 8);
