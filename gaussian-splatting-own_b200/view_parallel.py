@@ -7,15 +7,20 @@ optimizer — ONE exchange step, no other data-path collective.
 
 What is specific to this implementation:
 
-* the backward kernels write the five leaf gradients (means3D 3, sh 3M, opacity 1, scales 3,
-  rotations 4 floats per Gaussian = 59 at M = 16) into one contiguous arena
-  (diff_gaussian_rasterization/_C.py: rasterize_gaussians_backward), so the all-reduce runs IN
-  PLACE on the memory the kernels produced — no pack / unpack copies, one NCCL call for 708 MB at
-  3M Gaussians instead of five;
-* the collective is issued on the same stream right behind the backward, `async_op` optional, so
-  a trainer can overlap it with its loss bookkeeping.
+* the backward kernels write the five leaf gradients (means3D 3, opacity 1, scales 3, rotations 4,
+  sh 3M floats per Gaussian = 59 at M = 16) into one contiguous arena
+  (diff_gaussian_rasterization/_C.py: rasterize_gaussians_backward), so the exchange runs IN PLACE
+  on the memory the kernels produced — no pack / unpack copies;
+* exchange "nccl": one NCCL all-reduce of the arena (708 MB at 3M Gaussians) behind the backward,
+  `async_op` optional. The baseline, and what other backends (reference build, stubs) get;
+* exchange "nvls" (`NvlsExchange`, libbgr's own kernels over NVLink multicast): the backward
+  multicasts the 3-float SH-gradient factor per Gaussian while it computes, every rank rebuilds
+  dL_dsh locally, the other 11 floats are summed in the switch, and the whole exchange is
+  pipelined under the backward preprocess in Gaussian ranges (see the class docstring; DESIGN.md
+  §6 has the measurements: 0.21 / 0.23 / 0.33 ms per step at 2 / 4 / 8 GPUs instead of 1.3–1.9 ms).
 
-`torch.distributed` (NCCL on GPUs, gloo in the CPU tests) is plumbing only.
+`torch.distributed` (NCCL on GPUs, gloo in the CPU tests) and `torch.distributed._symmetric_memory`
+(allocation, rendezvous, barrier) are plumbing only.
 """
 from __future__ import annotations
 
@@ -27,6 +32,17 @@ import torch.distributed as dist
 LEAF_ORDER = ("means3D", "opacities", "scales", "rotations", "shs")   # memory order in the arena
 # index of each leaf's gradient in the 8-tuple returned by rasterize_gaussians_backward
 _GRAD_INDEX = {"means3D": 3, "shs": 5, "opacities": 2, "scales": 6, "rotations": 7}
+
+
+def chunk_bounds(P: int, chunks: int, align: int = 1024) -> list:
+    """[0, b1, ..., P]: at most `chunks` consecutive Gaussian ranges of equal size rounded up to
+    `align` (the multicast path needs bounds that are multiples of 4; 1024 keeps the ranges whole
+    blocks of the backward preprocess). The last range takes the remainder."""
+    if P <= 0:
+        return [0, 0]
+    chunks = max(1, int(chunks))
+    step = max(align, -(-(-(-P // chunks)) // align) * align)
+    return list(range(0, P, step)) + [P]
 
 
 def view_for_rank(step: int, world: int, rank: int, num_views: int) -> int:
@@ -130,8 +146,7 @@ class NvlsExchange:
         # multiples of 1024) and each finished range is exchanged on a second stream — barrier,
         # local dL_dsh rebuild, in-switch sum of its 11 floats/Gaussian — under the next range.
         self.chunks = max(1, int(chunks))
-        step = max(1024, -(-(-(-P // self.chunks)) // 1024) * 1024)   # ceil(P / chunks) rounded up to 1024
-        self.bounds = list(range(0, P, step)) + [P]
+        self.bounds = chunk_bounds(P, self.chunks)
         self._piped = False
         self.profile = False     # diagnostics: CUDA events around the pieces of all_reduce()
         self._marks = []

@@ -128,3 +128,20 @@ def test_product_never_imports_the_oracle():
                      r"#include\s+\"[^\"]*oracle", re.M)
     for f in list(pkg.rglob("*.py")) + list(pkg.rglob("*.cu")) + list(pkg.rglob("*.cuh")):
         assert not pat.search(f.read_text()), f"{f} reaches into oracle/"
+
+
+def test_bench_reads_roofline_traffic_from_the_committed_ncu_capture():
+    """bench.py's `roofline.traffic` comes from profiles/*_ncu_full_raw.csv (one launch of the
+    dominant kernel, DRAM read + write bytes); the file and the kernel rows must be there."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("bench_mod", ROOT / "bench.py")
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    assert (ROOT / bench.NCU_RAW).exists()
+    bwd = bench.ncu_traffic("render_backward")
+    fwd = bench.ncu_traffic("render_forward")
+    pre = bench.ncu_traffic("preprocess_backward")
+    assert isinstance(bwd, int) and 2e8 < bwd < 6e8          # ~357 MB at 3M Gaussians / 1080p
+    assert isinstance(fwd, int) and 1e8 < fwd < 4e8
+    assert isinstance(pre, int) and 1e9 < pre < 2e9          # ~1.41 GB: HBM-bound stage
+    assert bench.ncu_traffic("no_such_stage") is None

@@ -142,3 +142,16 @@ def test_view_dealing_covers_every_view_once_per_epoch():
     assert vp.view_for_rank(5, 8, 3, 7) == (5 * 8 + 3) % 7
     with pytest.raises(ValueError):
         vp.view_for_rank(0, 2, 0, 0)
+
+
+def test_chunk_bounds_for_the_pipelined_exchange():
+    for P, chunks in [(3_000_000, 2), (3_000_000, 4), (400_000, 2), (5000, 4), (1024, 4), (4, 2), (1_000_004, 3)]:
+        b = vp.chunk_bounds(P, chunks)
+        assert b[0] == 0 and b[-1] == P and len(b) - 1 <= chunks
+        assert all(x < y for x, y in zip(b[:-1], b[1:]))
+        assert all(x % 1024 == 0 for x in b[:-1])          # interior bounds: whole preprocess blocks
+        sizes = [y - x for x, y in zip(b[:-1], b[1:])]
+        assert max(sizes) - min(sizes[:-1] or sizes) <= 0 or len(sizes) == 1 or sizes[:-1].count(sizes[0]) == len(sizes) - 1
+    assert vp.chunk_bounds(0, 4) == [0, 0]
+    assert vp.chunk_bounds(3_000_000, 1) == [0, 3_000_000]
+    assert vp.chunk_bounds(3_000_000, 2) == [0, 1_500_160, 3_000_000]
