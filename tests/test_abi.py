@@ -145,3 +145,32 @@ def test_bench_reads_roofline_traffic_from_the_committed_ncu_capture():
     assert isinstance(fwd, int) and 1e8 < fwd < 4e8
     assert isinstance(pre, int) and 1e9 < pre < 2e9          # ~1.41 GB: HBM-bound stage
     assert bench.ncu_traffic("no_such_stage") is None
+
+
+def test_ctypes_structs_match_the_c_header_field_by_field(tmp_path):
+    """The argument blocks cross the boundary by layout, not by name: compile include/bgr.h as plain
+    C and compare sizeof / offsetof of every field with the ctypes mirrors in _C.py."""
+    import shutil
+    import subprocess
+    from diff_gaussian_rasterization import _C
+    gcc = shutil.which("gcc")
+    if gcc is None:
+        pytest.skip("no gcc")
+    pairs = (("BgrForwardArgs", _C._ForwardArgs), ("BgrBackwardArgs", _C._BackwardArgs))
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "bgr.h"', 'int main(void) {']
+    for cname, ct in pairs:
+        lines.append(f'  printf("{cname} %zu\\n", sizeof({cname}));')
+        for fname, _ in ct._fields_:
+            lines.append(f'  printf("{cname}.{fname} %zu\\n", offsetof({cname}, {fname}));')
+    lines += ['  return 0;', '}']
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "layout"
+    subprocess.run([gcc, "-std=c99", "-Wall", "-Werror", "-I", str(ROOT / "include"), str(src), "-o", str(exe)],
+                   check=True, capture_output=True)
+    got = dict(l.split() for l in subprocess.run([str(exe)], check=True, capture_output=True,
+                                                 text=True).stdout.splitlines())
+    for cname, ct in pairs:
+        assert int(got[cname]) == C.sizeof(ct), cname
+        for fname, _ in ct._fields_:
+            assert int(got[f"{cname}.{fname}"]) == getattr(ct, fname).offset, f"{cname}.{fname}"
