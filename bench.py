@@ -449,8 +449,8 @@ def cpu_baseline(wl):
     t2 = time.perf_counter()
     return {"value": round(1.0 / (t2 - t0), 5), "unit": "views/s", "cores": os.cpu_count(), "kind": "port",
             "sample": f"1 view fwd+bwd of the full workload ({wl.P} Gaussians, {wl.W}x{wl.H}); "
-                      f"forward {t1 - t0:.2f} s (OpenMP, all cores), backward {t2 - t1:.2f} s "
-                      f"(render backward is single-threaded)"}
+                      f"forward {t1 - t0:.2f} s, backward {t2 - t1:.2f} s (OpenMP over Gaussians / "
+                      f"tiles on all cores; the per-Gaussian gradient sums are a serial pass)"}
 
 
 def main():
