@@ -16,6 +16,8 @@ unsigned long long g_kernel_launches = 0;
 namespace {
 
 thread_local std::string g_last_error;
+// what the last bgr_forward on this thread decided (bgr_last_forward_info)
+thread_local int g_forward_info[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 
 int fail(int code, const std::string& msg)
 {
@@ -98,6 +100,7 @@ BGR_API const char* bgr_last_error(void) { return g_last_error.c_str(); }
 BGR_API const char* bgr_version(void) { return "bgr 0.1 (sm_100a)"; }
 
 BGR_API unsigned long long bgr_launch_count(void) { return bgr::g_kernel_launches; }
+BGR_API void bgr_last_forward_info(int* out8) { std::copy(g_forward_info, g_forward_info + 8, out8); }
 
 BGR_API void bgr_stage_timing(int enable)
 {
@@ -231,9 +234,12 @@ BGR_API int bgr_forward(const BgrForwardArgs* a, bgr_alloc_fn geom_alloc, void* 
         return rc;
     if ((rc = check_cuda(cudaStreamSynchronize(s), "sync after scan"))) return rc;
 
+    // the 64-bit total decides: the u32 scan wraps at 2^32 (the reference overflows silently,
+    // rasterizer_impl.cu:280-283)
+    if (host->tiles_total >= (1ull << 30))
+        return fail(BGR_ERR_OVERFLOW, "num_rendered = " + std::to_string(host->tiles_total) +
+                                          " >= 2^30 tile instances is not supported");
     const uint32_t R = host->num_rendered;
-    if (R >= (1u << 30))
-        return fail(BGR_ERR_OVERFLOW, "num_rendered >= 2^30 tile instances is not supported");
 
     const BinningLayout BL = binning_layout((size_t)R);
     unsigned char* bin = static_cast<unsigned char*>(binning_alloc(BL.total, binning_user));
@@ -263,6 +269,9 @@ BGR_API int bgr_forward(const BgrForwardArgs* a, bgr_alloc_fn geom_alloc, void* 
         uint32_t* vals_b = kf.pairs ? reinterpret_cast<uint32_t*>(bin + BL.vals_b) : nullptr;
         // emit into the buffer from which an odd/even number of passes ends in keys_a
         const int npasses = radix_sort_passes(kf.sort_lo, kf.sort_hi);
+        const int info[8] = {kf.pairs, kf.nb_idx, kf.nb_depth, kf.nb_tile, kf.sort_lo, kf.sort_hi,
+                             npasses, (int)R};
+        std::copy(info, info + 8, g_forward_info);
         const bool start_in_b = (npasses & 1) != 0;
         uint64_t* k_in = start_in_b ? keys_b : keys_a;
         uint64_t* k_alt = start_in_b ? keys_a : keys_b;
@@ -483,33 +492,6 @@ BGR_API int bgr_sh_grad_from_factors(int P, int D, int M, int world, const float
 {
     return bgr_sh_grad_from_factors_range(P, 0, P, D, M, world, means3D, campos_all, factors_all,
                                           dL_dsh, stream_v);
-}
-
-BGR_API int bgr_nvls_visibility_or(const int* radii, int P, uint32_t* local_words,
-                                   void* multicast_words, int rank, int world, int phase, void* stream_v)
-{
-    cudaStream_t s = static_cast<cudaStream_t>(stream_v);
-    if (P < 0 || (phase != 0 && phase != 1)) return fail(BGR_ERR_INVALID_ARG, "bad argument");
-    if (phase == 0) {
-        if (radii == nullptr || local_words == nullptr) return fail(BGR_ERR_INVALID_ARG, "NULL pointer");
-        bgr::launch_pack_visibility(radii, P, local_words, s);
-    } else if (bgr::launch_nvls_or(multicast_words, ((size_t)P + 31) / 32, rank, world, s) != 0) {
-        return fail(BGR_ERR_INVALID_ARG, "bad NVLS OR arguments");
-    }
-    return stage_check(false, s, "nvls visibility");
-}
-
-BGR_API int bgr_nvls_allreduce_rows_f32(void* multicast_a, int floats_a, void* multicast_b, int floats_b,
-                                        const uint32_t* vis_words, size_t rows, int rank, int world,
-                                        int max_blocks, void* stream_v)
-{
-    cudaStream_t s = static_cast<cudaStream_t>(stream_v);
-    if ((floats_a & 3) != 0 || (floats_b & 3) != 0)
-        return fail(BGR_ERR_INVALID_ARG, "row widths must be multiples of 4 floats");
-    if (bgr::launch_nvls_sparse_rows(multicast_a, floats_a / 4, multicast_b, floats_b / 4, vis_words, rows,
-                                     rank, world, max_blocks, s) != 0)
-        return fail(BGR_ERR_INVALID_ARG, "bad sparse NVLS arguments (NULL/unaligned pointer, rank, or row wider than 64 floats)");
-    return stage_check(false, s, "nvls sparse rows");
 }
 
 BGR_API size_t bgr_sort_temp_bytes(size_t n) { return bgr::sort_temp_layout(n).total; }

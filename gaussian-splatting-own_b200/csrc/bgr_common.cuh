@@ -30,8 +30,10 @@ struct GeomControl {
     uint32_t depth_max_bits; // max over visible Gaussians of float_as_uint(depth)
     uint32_t visible;        // number of Gaussians with radii > 0
     uint32_t scan_ticket;    // dynamic block id for the look-back scan
-    uint32_t pad[3];
+    uint32_t pad;
+    unsigned long long tiles_total;  // 64-bit sum of tiles_touched: the u32 scan total may wrap
 };
+static_assert(sizeof(GeomControl) == 32, "control block layout");
 
 struct GeomLayout {
     size_t rec, tiles, offsets, control, scan_state, total;
@@ -192,13 +194,9 @@ void launch_render_backward(int W, int H, const uint2* ranges, const uint32_t* p
 int launch_nvls_allreduce(void* multicast_ptr, size_t offset, size_t count, int rank, int world,
                           int max_blocks, cudaStream_t s);
 
-void launch_pack_visibility(const int* radii, int P, uint32_t* words, cudaStream_t s);
 int launch_nvls_allreduce_segments(void* multicast_ptr, int nseg, const size_t* offsets,
                                    const size_t* counts, int rank, int world, int max_blocks,
                                    cudaStream_t s);
-int launch_nvls_or(void* multicast_words, size_t nwords, int rank, int world, cudaStream_t s);
-int launch_nvls_sparse_rows(void* mc_a, int vecs_a, void* mc_b, int vecs_b, const uint32_t* vis_words,
-                            size_t rows, int rank, int world, int max_blocks, cudaStream_t s);
 
 struct PreprocessBackwardParams {
     int P, D, M, W, H;

@@ -174,27 +174,33 @@ __global__ void __launch_bounds__(PRE_THREADS, 4) preprocess_kernel(PreprocessPa
     // Depth range and visible count: reduced over the block first, so that the three counters
     // (one 32-byte sector in L2) receive one set of atomics per block instead of one per warp.
     __shared__ uint32_t s_lo[PRE_THREADS / 32], s_hi[PRE_THREADS / 32], s_cnt[PRE_THREADS / 32];
+    __shared__ uint32_t s_sum[PRE_THREADS / 32];   // <= 32 x tiles of one image: fits 32 bits
     const unsigned vis_mask = __ballot_sync(0xffffffffu, tiles != 0);
+    const uint32_t wsum = __reduce_add_sync(0xffffffffu, tiles);
     const uint32_t lo = __reduce_min_sync(0xffffffffu, tiles != 0 ? depth_bits : 0xffffffffu);
     const uint32_t hi = __reduce_max_sync(0xffffffffu, tiles != 0 ? depth_bits : 0u);
     if ((threadIdx.x & 31) == 0) {
         s_lo[threadIdx.x >> 5] = lo;
         s_hi[threadIdx.x >> 5] = hi;
         s_cnt[threadIdx.x >> 5] = (uint32_t)__popc(vis_mask);
+        s_sum[threadIdx.x >> 5] = wsum;
     }
     __syncthreads();
     if (threadIdx.x == 0) {
         uint32_t blo = 0xffffffffu, bhi = 0u, bcnt = 0u;
+        unsigned long long bsum = 0ull;
 #pragma unroll
         for (int w = 0; w < PRE_THREADS / 32; ++w) {
             blo = min(blo, s_lo[w]);
             bhi = max(bhi, s_hi[w]);
             bcnt += s_cnt[w];
+            bsum += s_sum[w];
         }
         if (bcnt != 0) {
             atomicMax(&p.control->depth_min_bits, ~blo);
             atomicMax(&p.control->depth_max_bits, bhi);
             atomicAdd(&p.control->visible, bcnt);
+            atomicAdd(&p.control->tiles_total, bsum);
         }
     }
 }

@@ -230,269 +230,6 @@ render_backward_kernel(int W, int H, const uint2* __restrict__ ranges,
     }
 }
 
-
-// ------------------------------------------------------------------------------------------------
-// Variant with TWO pixels per lane (opt-in: BGR_RENDER_2PX=1). A warp owns an 8x8 pixel block, lane
-// (lx, ly) the pixels (lx, ly) and (lx, ly + 4): the two 8x4 halves are exactly the blocks two
-// warps of the kernel above own. Most splats that touch one half touch the other, and the nine-value
-// warp reduction + REDs (54 of the ~150 instructions of an iteration above) are then paid once
-// per 8x8 block instead of once per 8x4 block. Per-pixel arithmetic, tests and traversal order are
-// unchanged, so the same (pixel, splat) pairs contribute; only the summation order differs.
-// ------------------------------------------------------------------------------------------------
-constexpr int R2_THREADS = 128;
-constexpr int R2_WARPS = R2_THREADS / 32;
-constexpr uint32_t R2_PLANE_BYTES = R2_THREADS * 16;
-
-struct PixelBwdState {
-    float T, T_final, accum0, accum1, accum2, last_alpha, lastc0, lastc1, lastc2, g0, g1, g2, bg_dot;
-};
-
-// One contributing (pixel, splat) pair: reference backward.cu:468-553, same expressions as the
-// one-pixel kernel above; the nine gradient terms are ADDED to v0..v8.
-__device__ __forceinline__ void pixel_pair_backward(PixelBwdState& s, float alpha, float G, float dx,
-                                                    float dy, float conx, float cony, float conz,
-                                                    float opacity, float cr, float cg, float cb,
-                                                    float ddelx_dx, float ddely_dy, float& v0, float& v1,
-                                                    float& v2, float& v3, float& v4, float& v5, float& v6,
-                                                    float& v7, float& v8)
-{
-    const float one_m_alpha = 1.f - alpha;
-    float rcp_oma;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rcp_oma) : "f"(one_m_alpha));
-    rcp_oma = __fmaf_rn(rcp_oma, __fmaf_rn(-one_m_alpha, rcp_oma, 1.0f), rcp_oma);
-    s.T = s.T * rcp_oma;
-    const float dchannel_dcolor = alpha * s.T;
-    float dL_dalpha = 0.0f;
-    const float one_m_last = 1.f - s.last_alpha;
-    s.accum0 = s.last_alpha * s.lastc0 + one_m_last * s.accum0;
-    s.lastc0 = cr;
-    dL_dalpha += (cr - s.accum0) * s.g0;
-    s.accum1 = s.last_alpha * s.lastc1 + one_m_last * s.accum1;
-    s.lastc1 = cg;
-    dL_dalpha += (cg - s.accum1) * s.g1;
-    s.accum2 = s.last_alpha * s.lastc2 + one_m_last * s.accum2;
-    s.lastc2 = cb;
-    dL_dalpha += (cb - s.accum2) * s.g2;
-    dL_dalpha *= s.T;
-    s.last_alpha = alpha;
-    dL_dalpha += (-s.T_final * rcp_oma) * s.bg_dot;
-
-    const float dL_dG = opacity * dL_dalpha;
-    const float gdx = G * dx;
-    const float gdy = G * dy;
-    const float dG_ddelx = -gdx * conx - gdy * cony;
-    const float dG_ddely = -gdy * conz - gdx * cony;
-    v0 += dL_dG * dG_ddelx * ddelx_dx;
-    v1 += dL_dG * dG_ddely * ddely_dy;
-    v2 += -0.5f * gdx * dx * dL_dG;
-    v3 += -0.5f * gdx * dy * dL_dG;
-    v4 += -0.5f * gdy * dy * dL_dG;
-    v5 += G * dL_dalpha;
-    v6 += dchannel_dcolor * s.g0;
-    v7 += dchannel_dcolor * s.g1;
-    v8 += dchannel_dcolor * s.g2;
-}
-
-__global__ void __launch_bounds__(R2_THREADS)
-render_backward_2px_kernel(int W, int H, const uint2* __restrict__ ranges,
-                           const uint32_t* __restrict__ point_list, const GaussRec* __restrict__ rec,
-                           const float* __restrict__ bg, const float* __restrict__ final_T,
-                           const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix,
-                           float* __restrict__ acc)
-{
-    __shared__ float4 s_rec[3 * R2_THREADS];   // planes: geo | opa | col
-    float4* const s_geo = s_rec;
-    float4* const s_opa = s_rec + R2_THREADS;
-    float4* const s_col = s_rec + 2 * R2_THREADS;
-    uint32_t s_base;
-    asm volatile("mov.u32 %0, %1;" : "=r"(s_base) : "r"((uint32_t)__cvta_generic_to_shared(s_rec)));
-    __shared__ uint32_t s_warp_count[R2_WARPS];
-    __shared__ uint32_t s_warp_max[R2_WARPS];
-
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t tiles_x = (W + TILE_X - 1) / TILE_X;
-    const uint32_t tile_px = blockIdx.x * TILE_X, tile_py = blockIdx.y * TILE_Y;
-    const uint32_t wpx = tile_px + ((warp & 1) << 3), wpy = tile_py + ((warp >> 1) << 3);
-    const uint32_t px = wpx + (lane & 7);
-    const uint32_t pyA = wpy + (lane >> 3), pyB = pyA + 4;
-    const bool insideA = px < (uint32_t)W && pyA < (uint32_t)H;
-    const bool insideB = px < (uint32_t)W && pyB < (uint32_t)H;
-    const size_t pixA = (size_t)pyA * W + px, pixB = (size_t)pyB * W + px;
-    const float pixfx = (float)px, pixfyA = (float)pyA, pixfyB = (float)pyB;
-    // tile rectangle (staging) and the two 8x4 halves of this warp (culling)
-    const float rx0 = (float)tile_px, ry0 = (float)tile_py;
-    const float rx1 = (float)min(tile_px + TILE_X - 1, (uint32_t)W - 1);
-    const float ry1 = (float)min(tile_py + TILE_Y - 1, (uint32_t)H - 1);
-    const float wx0 = (float)wpx, wx1 = (float)min(wpx + 7, (uint32_t)W - 1);
-    const float wyA0 = (float)wpy, wyA1 = (float)min(wpy + 3, (uint32_t)H - 1);
-    const float wyB0 = (float)(wpy + 4), wyB1 = (float)min(wpy + 7, (uint32_t)H - 1);
-
-    const uint2 range = ranges[blockIdx.y * tiles_x + blockIdx.x];
-
-    PixelBwdState A, B;
-    A.T_final = insideA ? final_T[pixA] : 0.0f;
-    B.T_final = insideB ? final_T[pixB] : 0.0f;
-    A.T = A.T_final;
-    B.T = B.T_final;
-    const uint32_t lastA = insideA ? n_contrib[pixA] : 0u;   // 0 => no splat is ever valid for it
-    const uint32_t lastB = insideB ? n_contrib[pixB] : 0u;
-
-    const uint32_t wmaxA = __reduce_max_sync(0xffffffffu, lastA);
-    const uint32_t wmaxB = __reduce_max_sync(0xffffffffu, lastB);
-    if (lane == 0) s_warp_max[warp] = max(wmaxA, wmaxB);
-    __syncthreads();
-    uint32_t total_u = 0;
-#pragma unroll
-    for (int w = 0; w < R2_WARPS; ++w) total_u = max(total_u, s_warp_max[w]);
-    total_u = min(total_u, range.y - range.x);
-    const int total = (int)total_u;
-    if (total == 0) return;
-    const int rounds = (total + R2_THREADS - 1) / R2_THREADS;
-
-    A.accum0 = A.accum1 = A.accum2 = A.last_alpha = A.lastc0 = A.lastc1 = A.lastc2 = 0.f;
-    B.accum0 = B.accum1 = B.accum2 = B.last_alpha = B.lastc0 = B.lastc1 = B.lastc2 = 0.f;
-    A.g0 = A.g1 = A.g2 = B.g0 = B.g1 = B.g2 = 0.f;
-    const size_t plane = (size_t)H * W;
-    if (insideA) {
-        A.g0 = dL_dpix[pixA];
-        A.g1 = dL_dpix[plane + pixA];
-        A.g2 = dL_dpix[2 * plane + pixA];
-    }
-    if (insideB) {
-        B.g0 = dL_dpix[pixB];
-        B.g1 = dL_dpix[plane + pixB];
-        B.g2 = dL_dpix[2 * plane + pixB];
-    }
-    const float bg0 = bg[0], bg1 = bg[1], bg2 = bg[2];
-    A.bg_dot = bg0 * A.g0 + bg1 * A.g1 + bg2 * A.g2;
-    B.bg_dot = bg0 * B.g0 + bg1 * B.g1 + bg2 * B.g2;
-    const float ddelx_dx = 0.5f * W;
-    const float ddely_dy = 0.5f * H;
-
-    for (int r = 0; r < rounds; ++r) {
-        __syncthreads();
-        const int progress = r * R2_THREADS + tid;
-        bool keep = false;
-        float4 q0, q1, q2;
-        uint32_t id = 0, li = 0;
-        if (progress < total) {
-            li = (uint32_t)(total - 1 - progress);  // back to front
-            id = point_list[range.x + li];
-            const GaussRec* g = rec + id;
-            q0 = __ldg(&g->q0);
-            q1 = __ldg(&g->q1);
-            q2 = __ldg(&g->q2);
-            keep = !tile_rejects(q0.x, q0.y, q0.z, q0.w, q1.x, q2.y, rx0, ry0, rx1, ry1);
-        }
-        const unsigned kmask = __ballot_sync(0xffffffffu, keep);
-        if (lane == 0) s_warp_count[warp] = __popc(kmask);
-        __syncthreads();
-        int before = 0, kept = 0;
-#pragma unroll
-        for (int w = 0; w < R2_WARPS; ++w) {
-            const int c = (int)s_warp_count[w];
-            if (w < warp) before += c;
-            kept += c;
-        }
-        if (keep) {
-            const int pos = before + __popc(kmask & ((1u << lane) - 1u));
-            s_geo[pos] = q0;
-            s_opa[pos] = make_float4(q1.x, q2.y, q1.y, __uint_as_float(li));
-            s_col[pos] = make_float4(q1.z, q1.w, q2.x, __uint_as_float(id));
-        }
-        __syncthreads();
-
-        for (int base = 0; base < kept; base += 32) {
-            const int jt = base + lane;
-            bool hitA = false, hitB = false;
-            if (jt < kept) {
-                const float4 ta = s_geo[jt];
-                const float4 tb = s_opa[jt];
-                const uint32_t tli = __float_as_uint(tb.w);
-                hitA = tli < wmaxA &&
-                       !tile_rejects(ta.x, ta.y, ta.z, ta.w, tb.x, tb.y, wx0, wyA0, wx1, wyA1);
-                hitB = tli < wmaxB &&
-                       !tile_rejects(ta.x, ta.y, ta.z, ta.w, tb.x, tb.y, wx0, wyB0, wx1, wyB1);
-            }
-            const unsigned hitsA = __ballot_sync(0xffffffffu, hitA);
-            const unsigned hitsB = __ballot_sync(0xffffffffu, hitB);
-            unsigned hits = hitsA | hitsB;
-            while (hits) {
-                const int bit = __ffs(hits) - 1;
-                hits &= hits - 1;
-                const bool inA = (hitsA >> bit) & 1u;   // warp-uniform
-                const bool inB = (hitsB >> bit) & 1u;
-                const uint32_t ja = s_base + 16u * (uint32_t)(base + bit);
-                const float4 a = lds128(ja);
-                const float4 o = lds128(ja + R2_PLANE_BYTES);
-                const uint32_t pos_in_list = __float_as_uint(o.w);
-                const float dx = a.x - pixfx;
-                float dyA = 0.f, dyB = 0.f, powerA = 0.f, powerB = 0.f;
-                bool validA = false, validB = false;
-                if (inA) {
-                    dyA = a.y - pixfyA;
-                    powerA = gauss_power(a.z, a.w, o.x, dx, dyA);
-                    validA = pos_in_list < lastA && !(powerA > 0.0f || powerA < o.y);
-                }
-                if (inB) {
-                    dyB = a.y - pixfyB;
-                    powerB = gauss_power(a.z, a.w, o.x, dx, dyB);
-                    validB = pos_in_list < lastB && !(powerB > 0.0f || powerB < o.y);
-                }
-                if (!__any_sync(0xffffffffu, validA || validB)) continue;
-                float GA = 0.f, GB = 0.f, alphaA = 0.f, alphaB = 0.f;
-                if (inA) {
-                    GA = expf(powerA);
-                    alphaA = fminf(0.99f, o.z * GA);
-                    validA = validA && !(alphaA < 1.0f / 255.0f);
-                }
-                if (inB) {
-                    GB = expf(powerB);
-                    alphaB = fminf(0.99f, o.z * GB);
-                    validB = validB && !(alphaB < 1.0f / 255.0f);
-                }
-                if (!__any_sync(0xffffffffu, validA || validB)) continue;
-                const float4 c = lds128(ja + 2 * R2_PLANE_BYTES);
-
-                float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f, v4 = 0.f, v5 = 0.f, v6 = 0.f, v7 = 0.f,
-                      v8 = 0.f;
-                if (validA)
-                    pixel_pair_backward(A, alphaA, GA, dx, dyA, a.z, a.w, o.x, o.z, c.x, c.y, c.z,
-                                        ddelx_dx, ddely_dy, v0, v1, v2, v3, v4, v5, v6, v7, v8);
-                if (validB)
-                    pixel_pair_backward(B, alphaB, GB, dx, dyB, a.z, a.w, o.x, o.z, c.x, c.y, c.z,
-                                        ddelx_dx, ddely_dy, v0, v1, v2, v3, v4, v5, v6, v7, v8);
-
-                // same transposing butterfly as the one-pixel kernel
-                const bool h1 = (lane & 16) != 0;
-                float w0 = (h1 ? v4 : v0) + __shfl_xor_sync(0xffffffffu, h1 ? v0 : v4, 16);
-                float w1 = (h1 ? v5 : v1) + __shfl_xor_sync(0xffffffffu, h1 ? v1 : v5, 16);
-                float w2 = (h1 ? v6 : v2) + __shfl_xor_sync(0xffffffffu, h1 ? v2 : v6, 16);
-                float w3 = (h1 ? v7 : v3) + __shfl_xor_sync(0xffffffffu, h1 ? v3 : v7, 16);
-                const bool h2 = (lane & 8) != 0;
-                float u0 = (h2 ? w2 : w0) + __shfl_xor_sync(0xffffffffu, h2 ? w0 : w2, 8);
-                float u1 = (h2 ? w3 : w1) + __shfl_xor_sync(0xffffffffu, h2 ? w1 : w3, 8);
-                const bool h3 = (lane & 4) != 0;
-                float sacc = (h3 ? u1 : u0) + __shfl_xor_sync(0xffffffffu, h3 ? u0 : u1, 4);
-                v8 += __shfl_xor_sync(0xffffffffu, v8, 16);
-                v8 += __shfl_xor_sync(0xffffffffu, v8, 8);
-                v8 += __shfl_xor_sync(0xffffffffu, v8, 4);
-                const bool h4 = (lane & 2) != 0;
-                float fin = (h4 ? v8 : sacc) + __shfl_xor_sync(0xffffffffu, h4 ? sacc : v8, 2);
-                fin += __shfl_xor_sync(0xffffffffu, fin, 1);
-
-                float* row = acc + (size_t)__float_as_uint(c.w) * ACC_STRIDE;
-                if ((lane & 3) == 0) {
-                    const int vi = ((lane >> 2) & 1) | (((lane >> 3) & 1) << 1) | (((lane >> 4) & 1) << 2);
-                    atomicAdd(row + vi, fin);
-                } else if (lane == 2) {
-                    atomicAdd(row + 8, fin);
-                }
-            }
-        }
-    }
-}
-
 }  // namespace
 
 void launch_render_backward(int W, int H, const uint2* ranges, const uint32_t* point_list,
@@ -502,16 +239,6 @@ void launch_render_backward(int W, int H, const uint2* ranges, const uint32_t* p
 {
     const dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1);
     ++g_kernel_launches;
-    // experimental two-pixels-per-lane variant, opt-in until it has its own parity + ncu record
-    static const bool two_px = [] {
-        const char* e = std::getenv("BGR_RENDER_2PX");
-        return e != nullptr && e[0] == '1';
-    }();
-    if (two_px) {
-        render_backward_2px_kernel<<<grid, R2_THREADS, 0, s>>>(W, H, ranges, point_list, rec, bg, final_T,
-                                                               n_contrib, dL_dpix, acc);
-        return;
-    }
     render_backward_kernel<<<grid, RENDER_THREADS, 0, s>>>(W, H, ranges, point_list, rec, bg, final_T,
                                                           n_contrib, dL_dpix, acc);
 }

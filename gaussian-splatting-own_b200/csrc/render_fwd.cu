@@ -175,8 +175,6 @@ render_forward_kernel(int W, int H, const uint2* __restrict__ ranges,
     }
 }
 
-#include "render_fwd_2px.cuh"
-
 }  // namespace
 
 void launch_render_forward(int W, int H, const uint2* ranges, const uint32_t* point_list,
@@ -185,16 +183,6 @@ void launch_render_forward(int W, int H, const uint2* ranges, const uint32_t* po
 {
     const dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1);
     ++g_kernel_launches;
-    // experimental two-pixels-per-lane variant, opt-in until it has its own parity + ncu record
-    static const bool two_px = [] {
-        const char* e = std::getenv("BGR_RENDER_2PX");
-        return e != nullptr && e[0] == '1';
-    }();
-    if (two_px) {
-        render_forward_2px_kernel<<<grid, F2_THREADS, 0, s>>>(W, H, ranges, point_list, rec, bg, final_T,
-                                                              n_contrib, out_color);
-        return;
-    }
     render_forward_kernel<false><<<grid, RENDER_THREADS, 0, s>>>(W, H, ranges, point_list, rec, bg,
                                                                 final_T, n_contrib, out_color,
                                                                 nullptr);

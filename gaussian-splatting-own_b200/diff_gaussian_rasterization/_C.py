@@ -109,14 +109,10 @@ def lib() -> C.CDLL:
     L.bgr_nvls_allreduce_segments_f32.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_size_t),
                                                   C.POINTER(C.c_size_t), C.c_int, C.c_int, C.c_int,
                                                   C.c_void_p]
-    L.bgr_nvls_visibility_or.restype = C.c_int
-    L.bgr_nvls_visibility_or.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
-                                         C.c_int, C.c_void_p]
-    L.bgr_nvls_allreduce_rows_f32.restype = C.c_int
-    L.bgr_nvls_allreduce_rows_f32.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p,
-                                              C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_void_p]
     L.bgr_launch_count.restype = C.c_ulonglong
     L.bgr_launch_count.argtypes = []
+    L.bgr_last_forward_info.restype = None
+    L.bgr_last_forward_info.argtypes = [C.POINTER(C.c_int)]
     L.bgr_stage_timing.restype = None
     L.bgr_stage_timing.argtypes = [C.c_int]
     L.bgr_stage_count.restype = C.c_int
@@ -390,23 +386,6 @@ def nvls_allreduce_segments(multicast_ptr: int, segments, rank: int, world: int,
                                                      max_blocks, _stream(device)))
 
 
-def nvls_visibility(radii, P: int, local_words_ptr: int, multicast_words_ptr: int, rank: int,
-                    world: int, phase: int, device) -> None:
-    with torch.cuda.device(device):
-        _check(lib().bgr_nvls_visibility_or(C.c_void_p(radii.data_ptr() if radii is not None else None),
-                                            int(P), C.c_void_p(local_words_ptr),
-                                            C.c_void_p(multicast_words_ptr), rank, world, phase,
-                                            _stream(device)))
-
-
-def nvls_allreduce_rows(mc_a: int, floats_a: int, mc_b: int, floats_b: int, vis_words_ptr: int,
-                        rows: int, rank: int, world: int, device, max_blocks: int = 296) -> None:
-    with torch.cuda.device(device):
-        _check(lib().bgr_nvls_allreduce_rows_f32(C.c_void_p(mc_a), floats_a, C.c_void_p(mc_b), floats_b,
-                                                 C.c_void_p(vis_words_ptr), rows, rank, world,
-                                                 max_blocks, _stream(device)))
-
-
 def leaf_grad_arena(grads) -> torch.Tensor:
     """The flat f32 tensor that aliases (dL_dmeans3D, dL_dopacity, dL_dscales, dL_drotations,
     dL_dsh) of one rasterize_gaussians_backward result, in that (memory) order."""
@@ -423,6 +402,13 @@ def leaf_grad_arena(grads) -> torch.Tensor:
 # ---- diagnostics -------------------------------------------------------------------------------
 def launch_count() -> int:
     return int(lib().bgr_launch_count())
+
+
+def last_forward_info() -> dict:
+    out = (C.c_int * 8)()
+    lib().bgr_last_forward_info(out)
+    return dict(zip(("pairs", "nb_idx", "nb_depth", "nb_tile", "sort_lo", "sort_hi", "passes", "R"),
+                    [int(x) for x in out]))
 
 
 def stage_timing(enable: bool) -> None:

@@ -96,11 +96,9 @@ class NvlsExchange:
         identical everywhere) and only the remaining 11 floats/Gaussian are summed in the switch.
         Fabric traffic at 3M Gaussians, 8 GPUs: 36 MB out + 252 MB in (overlapped with the
         backward) + a 132 MB in-switch sum, instead of a 708 MB all-reduce.
-    mode "rows": the small leaves densely, rotations + sh only for rows some rank sees.
-    mode "dense": the whole 59-float block in the switch."""
+    mode "dense": the whole 59-float block in the switch (fallback when P % 4 != 0 or M == 0)."""
 
     NON_LEAF_FLOATS = 12   # means2D 3 + colors 3 + cov3D 6 precede the leaf block in the arena
-    DENSE_FLOATS = 7       # means3D 3 + opacity 1 + scales 3
     SMALL_FLOATS = 11      # ... + rotations 4: everything except sh
 
     def __init__(self, P: int, M: int, device, group: Optional[dist.ProcessGroup] = None,
@@ -115,22 +113,18 @@ class NvlsExchange:
         grp = group if group is not None else dist.group.WORLD
         world = dist.get_world_size(grp)
         up4 = lambda n: (n + 3) // 4 * 4  # noqa: E731
-        self.words_off = up4(self.numel)
-        self.nwords = (P + 31) // 32
-        self.campos_off = self.words_off + up4(self.nwords)
+        self.campos_off = up4(self.numel)
         self.factors_off = self.campos_off + 4 * world
         aligned = P % 4 == 0
+        if mode not in ("factor", "dense"):
+            raise ValueError("mode must be 'factor' or 'dense'")
         if mode == "factor" and not (aligned and M > 0):
-            mode = "rows"
-        if mode == "rows" and not (aligned and (3 * M) % 4 == 0 and 0 < 4 + 3 * M <= 64):
             mode = "dense"
-        if mode not in ("factor", "rows", "dense"):
-            raise ValueError("mode must be 'factor', 'rows' or 'dense'")
         self.mode = mode
         # CTAs of the in-switch sum. Mode "factor" runs it BESIDE the HBM-bound dL_dsh rebuild and
         # the next range's preprocess: its multimem requests are slow (fabric round trips) and, with
         # a CTA on every SM, starve the other kernels' loads (measured: rebuild 0.14 -> 0.48 ms).
-        # 32 CTAs keep the fabric as busy and leave 116 SMs alone. Alone (rows / dense) it gets 296.
+        # 32 CTAs keep the fabric as busy and leave 116 SMs alone. Alone (dense) it gets 296.
         self.max_blocks = self._max_blocks_arg if self._max_blocks_arg is not None else \
             (32 if mode == "factor" else 296)
         total = self.factors_off + (world * P * 3 if mode == "factor" else 0)
@@ -139,7 +133,6 @@ class NvlsExchange:
         if not self.hdl.multicast_ptr:
             raise RuntimeError("NVLink multicast (NVLS) is not available for this group")
         self.rank, self.world = self.hdl.rank, self.hdl.world_size
-        self._have_mask = False
         self._pending = None     # (D, means3D, dL_dsh) of the backward whose factors are in flight
         self._side = self._side2 = None
         # mode "factor": the backward preprocess runs in `chunks` Gaussian ranges (bounds are
@@ -201,26 +194,7 @@ class NvlsExchange:
             self._side = torch.cuda.Stream(self.device, priority=-1)   # in-switch sums
             self._side2 = torch.cuda.Stream(self.device)                # local dL_dsh rebuild
 
-    @property
-    def sparse(self):
-        return self.mode == "rows"
-
-    @sparse.setter
-    def sparse(self, v):     # used by tests/dp_check.py to compare the modes on one instance
-        if self.mode != "factor":
-            self.mode = "rows" if v else "dense"
-
     # ---- the exchange ------------------------------------------------------------------------
-    def begin(self, radii: torch.Tensor) -> None:
-        """After the forward (mode "rows" only): visibility bits -> OR over ranks in the switch."""
-        if self.mode != "rows":
-            return
-        mc, local = self.hdl.multicast_ptr + 4 * self.words_off, self.buf.data_ptr() + 4 * self.words_off
-        self._C.nvls_visibility(radii, self.P, local, mc, self.rank, self.world, 0, self.device)
-        self.hdl.barrier(channel=0)
-        self._C.nvls_visibility(None, self.P, local, mc, self.rank, self.world, 1, self.device)
-        self._have_mask = True   # made visible to every rank by the barrier at the start of all_reduce
-
     def all_reduce(self) -> None:
         """Sum of the leaf block across ranks, in place, on the current stream."""
         P, mc = self.P, self.hdl.multicast_ptr
@@ -269,16 +243,8 @@ class NvlsExchange:
             cur.wait_stream(self._side2)
             mark("sh_rebuild_tail")
             self._pending = None
-        elif self.mode == "rows" and self._have_mask:
-            red(leaf0, P * self.DENSE_FLOATS)
-            rot0 = leaf0 + P * self.DENSE_FLOATS
-            sh0 = rot0 + 4 * P
-            self._C.nvls_allreduce_rows(mc + 4 * rot0, 4, mc + 4 * sh0, 3 * self.M,
-                                        self.buf.data_ptr() + 4 * self.words_off, P, self.rank,
-                                        self.world, self.device, self.max_blocks)
         else:
             red(leaf0, P * self.leaf_floats)
-        self._have_mask = False
         self.hdl.barrier(channel=0)        # sums broadcast everywhere; factor slots free for reuse
         mark("barrier_out")
 
@@ -356,8 +322,6 @@ class ViewParallelRasterizer:
         R, color, radii, geom, binning, img = fwd
         if self.exchange == "nvls" and self.world > 1 and self._nvls is None:
             self._nvls = NvlsExchange(scene["means3D"].size(0), scene["shs"].size(1), dev, self.group)
-        if self._nvls is not None:
-            self._nvls.begin(radii)
         dL_dpix = loss_grad(color)
         if self.average and self.world > 1:
             dL_dpix = dL_dpix / self.world     # fold the 1/G of a mean into the upstream gradient

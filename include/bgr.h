@@ -44,7 +44,8 @@ extern "C" {
 #define BGR_ERR_INVALID_ARG   -1   /* bad shape / NULL where data is required              */
 #define BGR_ERR_CUDA          -2   /* a CUDA runtime call or (debug mode) a kernel failed   */
 #define BGR_ERR_ALLOC         -3   /* an allocator callback returned NULL                   */
-#define BGR_ERR_OVERFLOW      -4   /* num_rendered >= 2^31 (reference overflows silently,   */
+#define BGR_ERR_OVERFLOW      -4   /* num_rendered >= 2^30 tile instances, counted in 64    */
+                                   /* bits (the reference overflows its int silently,       */
                                    /* rasterizer_impl.cu:280-283)                           */
 
 /* Grows (or allocates) a scratch buffer to `bytes` and returns its device address. */
@@ -194,20 +195,13 @@ BGR_API int bgr_nvls_allreduce_segments_f32(void* multicast_ptr, int nseg, const
                                             const size_t* counts_floats, int rank, int world,
                                             int max_blocks, void* stream);
 
-/* Row-sparse variant. A Gaussian that no rank sees has an all-zero gradient row everywhere and need
- * not cross the fabric. phase 0: packs (radii > 0) into one bit per Gaussian in local_words (part of
- * the symmetric buffer); [cross-GPU barrier]; phase 1: ORs the words across ranks in the switch. */
-BGR_API int bgr_nvls_visibility_or(const int* radii, int P, uint32_t* local_words,
-                                   void* multicast_words, int rank, int world, int phase, void* stream);
-/* Sums, across ranks, only the rows whose bit is set in vis_words, of two row-major blocks sharing
- * the row index (a: floats_a per row, b: floats_b per row; multiples of 4, at most 64 in total). */
-BGR_API int bgr_nvls_allreduce_rows_f32(void* multicast_a, int floats_a, void* multicast_b, int floats_b,
-                                        const uint32_t* vis_words, size_t rows, int rank, int world,
-                                        int max_blocks, void* stream);
-
 /* ---- diagnostics (bench.py / tests; nothing here is on the product path) --------------------- */
 /* Total number of CUDA kernels this library has launched in this process. */
 BGR_API unsigned long long bgr_launch_count(void);
+/* Key format the last bgr_forward on the calling thread chose (only when num_rendered > 0):
+ * [0] 1 = separate u32 values ("pairs": index + depth + tile bits exceed 64), 0 = packed keys,
+ * [1] index bits [2] depth bits [3] tile bits [4],[5] sorted bit range [6] sort passes [7] R. */
+BGR_API void bgr_last_forward_info(int* out8);
 /* Per-stage CUDA-event timing on the launch stream: enable, run bgr_forward / bgr_backward, then
  * read the durations (ms; -1 for a stage that did not run). Stage i is named bgr_stage_name(i). */
 BGR_API void bgr_stage_timing(int enable);

@@ -4,8 +4,8 @@ from /root/reference (possible only in the build container, on the CPU):
   utils/sh_utils.py:57-112         eval_sh          -> SH colour of random directions, degrees 0..3
   utils/graphics_utils.py:38-71    getWorld2View2, getProjectionMatrix -> camera matrices
 
-The committed .npz pins oracle/rasterizer_oracle.c (sh_rgb) and gaussian-splatting-own_b200/
-synthetic.py (world_to_view, projection_matrix, make_camera) against the reference.
+The committed .npz pins oracle/rasterizer_oracle.c (sh_rgb) and tests/synthetic.py
+(rigid_world_to_camera, perspective, make_camera) against the reference.
 
     python tests/golden/make_golden_cpu.py
 """

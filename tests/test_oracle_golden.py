@@ -94,7 +94,7 @@ def test_oracle_sh_matches_reference_eval_sh():
     import torch
     view = torch.eye(4)
     view[3, 2] = 50.0
-    cam = cam._replace(viewmatrix=view, projmatrix=view @ synthetic.projection_matrix(
+    cam = cam._replace(viewmatrix=view, projmatrix=view @ synthetic.perspective(
         0.01, 100.0, 1.0, 1.0).T, campos=torch.tensor(campos))
     scene = dict(means3D=means, shs=shs, opacities=np.full((P, 1), 0.5, np.float32),
                  scales=np.full((P, 3), 0.5, np.float32),
