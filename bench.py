@@ -52,6 +52,14 @@ def parse_args():
     ap.add_argument("--impl", choices=("ours", "reference"), default="ours")
     ap.add_argument("--gaussians", type=int, default=3_000_000)
     ap.add_argument("--res", choices=("800x800", "1080p", "4k"), default="1080p")
+    ap.add_argument("--mode", choices=("step", "sweep"), default="step",
+                    help="step: the train-step bench (default). sweep: BASELINE.json configs[4], the "
+                         "forward-only 4K grid over Gaussians x SH degree x scale_modifier, both arms "
+                         "per cell, written to --out")
+    ap.add_argument("--sweep-gaussians", default="1,2,5,10", help="millions of Gaussians per cell")
+    ap.add_argument("--sweep-degrees", default="0,3")
+    ap.add_argument("--sweep-mods", default="0.5,1,2")
+    ap.add_argument("--out", default="gpurun_out/sweep_4k.json")
     ap.add_argument("--skip-cpu-baseline", action="store_true")
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--chunks", type=int, default=2,
@@ -59,7 +67,7 @@ def parse_args():
                          "against the exchange in (1 = exchange after the backward)")
     ap.add_argument("--nvls-blocks", type=int, default=0,
                     help="CTAs of the in-switch sum kernel (0 = the exchange mode's default)")
-    ap.add_argument("--exchange", choices=("nvls", "nvls-rows", "nvls-dense", "nccl"), default="nvls",
+    ap.add_argument("--exchange", choices=("nvls", "nvls-dense", "nccl"), default="nvls",
                     help="N > 1, ours: in-switch multimem kernel of libbgr (default) or ncclAllReduce")
     return ap.parse_args()
 
@@ -172,7 +180,7 @@ def make_native_step(backend, wl, world, impl, exchange="nccl", chunks=2, nvls_b
     if world > 1 and impl == "ours" and exchange.startswith("nvls"):
         try:
             nvls = vp.NvlsExchange(wl.P, 16, wl.device,
-                                   mode={"nvls": "factor", "nvls-rows": "rows", "nvls-dense": "dense"}[exchange],
+                                   mode={"nvls": "factor", "nvls-dense": "dense"}[exchange],
                                    chunks=chunks, max_blocks=nvls_blocks or None)
             ok = torch.ones(1, device=wl.device)
         except Exception as e:  # no NVLink multicast / symmetric memory on this box
@@ -188,11 +196,12 @@ def make_native_step(backend, wl, world, impl, exchange="nccl", chunks=2, nvls_b
                   "using the NCCL all-reduce of the gradient arena", file=sys.stderr)
     make_native_step.nvls = nvls
 
+    import contextlib
+
     def step():
         out = backend.rasterize_gaussians(*wl.fwd_args())
-        if nvls is not None:
-            nvls.begin(out[2])                                        # visibility OR over ranks
-        grads = backend.rasterize_gaussians_backward(*wl.bwd_args(out))
+        with (nvls if nvls is not None else contextlib.nullcontext()):   # outputs -> symmetric arena
+            grads = backend.rasterize_gaussians_backward(*wl.bwd_args(out))
         if world > 1:
             if nvls is not None:
                 nvls.all_reduce()                                     # in-switch sum, own kernel
@@ -200,9 +209,10 @@ def make_native_step(backend, wl, world, impl, exchange="nccl", chunks=2, nvls_b
                 flat, aliased = vp.flat_leaf_gradients(grads)         # zero-copy view of the arena
                 assert aliased
                 dist.all_reduce(flat)                                 # in place, one collective
-            else:
-                for t in (grads[3], grads[5], grads[2], grads[6], grads[7]):
-                    dist.all_reduce(t)
+            else:                                                     # packed: one collective too
+                flat, _ = vp.flat_leaf_gradients(grads)
+                dist.all_reduce(flat)
+                vp.scatter_flat(flat, grads)
         return out, grads
     return step
 
@@ -236,6 +246,8 @@ def make_e2e_step(backend, wl, world, impl):
     copy_stream = torch.cuda.Stream(device=dev)
     w_ready = torch.cuda.Event()
 
+    nvls = getattr(make_native_step, "nvls", None) if world > 1 else None
+
     def step():
         cam_dev.copy_(cam_host, non_blocking=True)
         with torch.cuda.stream(copy_stream):
@@ -253,19 +265,26 @@ def make_e2e_step(backend, wl, world, impl):
             means3D=leaves["means3D"], means2D=means2D, shs=leaves["shs"], colors_precomp=None,
             opacities=leaves["opacities"], scales=leaves["scales"], rotations=leaves["rotations"],
             cov3D_precomp=None)
-        nvls = getattr(make_native_step, "nvls", None) if world > 1 else None
-        if nvls is not None:
-            nvls.begin(radii_)
         torch.cuda.current_stream().wait_event(w_ready)
         loss = (color * w_dev).sum()
-        loss.backward()
-        if world > 1:
+        if nvls is not None:
+            with nvls:                 # the backward writes into the symmetric arena
+                loss.backward()
             g0 = leaves["means3D"].grad
-            if nvls is not None and g0.data_ptr() == nvls.buf.data_ptr() + 4 * 12 * wl.P:
-                nvls.all_reduce()      # autograd handed out views of the symmetric arena: in place
-            else:
+            if g0.data_ptr() != nvls.buf.data_ptr() + 4 * 12 * wl.P:
+                # autograd copied instead of handing out views of the arena: the in-place exchange
+                # would not reach the leaves' .grad. Never time a numerically wrong step.
+                raise RuntimeError("e2e: leaf gradients do not alias the exchange arena")
+            nvls.all_reduce()          # in place, in the switch
+        else:
+            loss.backward()
+            if world > 1:              # one collective over the flattened leaf gradients
+                flat = torch.cat([t.grad.reshape(-1) for t in leaves.values()])
+                dist.all_reduce(flat)
+                o = 0
                 for t in leaves.values():
-                    dist.all_reduce(t.grad)
+                    t.grad.copy_(flat[o:o + t.grad.numel()].view_as(t.grad))
+                    o += t.grad.numel()
         loss_host.copy_(loss.detach(), non_blocking=True)
         torch.cuda.current_stream().synchronize()
         return float(loss_host)
@@ -453,6 +472,101 @@ def cpu_baseline(wl):
                       f"tiles on all cores; the per-Gaussian gradient sums are a serial pass)"}
 
 
+# --------------------------------------------------------------------------------------------
+# configs[4]: render-only sweep at 3840x2160 (tile-list length and sort-size stress)
+# --------------------------------------------------------------------------------------------
+def run_sweep(args, device):
+    """Forward only, both arms per cell on the same inputs: P x SH degree x scale_modifier at 4K.
+    Per cell: visible Gaussians, tile instances R, mean / max tile list, the key format libbgr
+    chose, per-stage ms of libbgr (CUDA events inside the library), ms per forward of each arm
+    (CUDA events, 3 warm-up + 8 timed), and the parity of the two arms' outputs (integer buffers
+    bit-equal, image max-abs difference)."""
+    import synthetic
+    import util
+    ours = load_backend("ours")
+    ref = load_backend("reference")
+    W, H, focal = synthetic.RESOLUTIONS[args.res if args.res != "1080p" else "4k"]
+    cam = synthetic.make_camera(W, H, focal)
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    bg = torch.zeros(3, device=device)
+    cells = []
+    for pm in [float(x) for x in args.sweep_gaussians.split(",")]:
+        P = int(round(pm * 1e6))
+        scene = {k: v.to(device) for k, v in synthetic.make_gaussians(P, seed=0).items()}
+        for deg in [int(x) for x in args.sweep_degrees.split(",")]:
+            for mod in [float(x) for x in args.sweep_mods.split(",")]:
+                def fwd(backend):
+                    return util.native_forward(backend, scene, cam, bg, deg, mod)[1]
+
+                def time_arm(backend, n_warm=3, n=8):
+                    for _ in range(n_warm):
+                        out = fwd(backend)
+                    torch.cuda.synchronize(device)
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record()
+                    for _ in range(n):
+                        out = fwd(backend)
+                    e1.record()
+                    torch.cuda.synchronize(device)
+                    return e0.elapsed_time(e1) / n, out
+
+                ms_ours, out = time_arm(ours)
+                ours.stage_timing(True)
+                acc = {}
+                for _ in range(3):
+                    fwd(ours)
+                    torch.cuda.synchronize(device)
+                    for k, v in ours.stage_times().items():
+                        acc[k] = acc.get(k, 0.0) + v / 3
+                ours.stage_timing(False)
+                info = ours.last_forward_info()
+                R = int(out[0])
+                m = util.bgr_intermediates(out, P, W, H)
+                lens = (m["ranges"][:, 1] - m["ranges"][:, 0]).long()
+                st = ours.render_stats(out, P, W, H)
+                cell = {"gaussians": P, "sh_degree": deg, "scale_modifier": mod,
+                        "visible": int((out[2] > 0).sum()), "num_rendered": R,
+                        "mean_tile_list": round(R / tiles, 1), "max_tile_list": int(lens.max()),
+                        "sum_n_contrib": int(m["n_contrib"].long().sum()),
+                        "key_format": {"pairs": info["pairs"], "index_bits": info["nb_idx"],
+                                       "depth_bits": info["nb_depth"], "tile_bits": info["nb_tile"],
+                                       "sort_passes": info["passes"]},
+                        "ours_ms": round(ms_ours, 4), "ours_stage_ms": {k: round(v, 4) for k, v in acc.items()},
+                        "pairs_examined": st["examined"], "pairs_blended": st["blended"]}
+                if ref is not None:
+                    ms_ref, o_r = time_arm(ref)
+                    im = ref.parse_img(o_r[5], W, H)
+                    b = ref.parse_binning(o_r[4], o_r[0])
+                    cell["reference_ms"] = round(ms_ref, 4)
+                    cell["speedup"] = round(ms_ref / ms_ours, 3)
+                    cell["parity"] = {
+                        "num_rendered": int(o_r[0]) == R,
+                        "radii": bool(torch.equal(o_r[2], out[2])),
+                        "point_list": bool(torch.equal(b["point_list"], m["point_list"])),
+                        "ranges": bool(torch.equal(im["ranges"][:tiles], m["ranges"])),
+                        "n_contrib": bool(torch.equal(im["n_contrib"], m["n_contrib"])),
+                        "image_max_abs_diff": float((o_r[1] - out[1]).abs().max()),
+                    }
+                    del o_r, im, b
+                cells.append(cell)
+                print(json.dumps(cell), file=sys.stderr, flush=True)
+                del out, m
+        del scene
+        torch.cuda.empty_cache()
+    doc = {"config": f"BASELINE.json configs[4]: render-only sweep at {W}x{H}, seeded scene of SURVEY.md 8d, "
+                     "forward only, inputs resident", "gpu": torch.cuda.get_device_name(device),
+           "reference": "oracle/_ref (the reference's unmodified .cu files, sm_100a)" if ref is not None else None,
+           "cells": cells}
+    out_path = Path(args.out)
+    out_path.parent.mkdir(parents=True, exist_ok=True)
+    out_path.write_text(json.dumps(doc, indent=1))
+    ok = all(all(v is True or (k == "image_max_abs_diff" and v <= 1e-5) for k, v in c.get("parity", {}).items())
+             for c in cells)
+    print(json.dumps({"mode": "sweep", "cells": len(cells), "parity_all_cells": ok, "out": str(out_path),
+                      "speedup_min": min((c.get("speedup", 0) for c in cells), default=None),
+                      "speedup_max": max((c.get("speedup", 0) for c in cells), default=None)}))
+
+
 def main():
     args = parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -477,6 +591,12 @@ def main():
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=device)
+
+    if args.mode == "sweep":
+        if world > 1:
+            raise SystemExit("--mode sweep is a single-GPU run")
+        run_sweep(args, device)
+        return
 
     wl = Workload(args, rank, device)
     native = make_native_step(backend, wl, world, args.impl, args.exchange, args.chunks, args.nvls_blocks)

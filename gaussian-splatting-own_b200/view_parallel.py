@@ -144,9 +144,26 @@ class NvlsExchange:
         self.profile = False     # diagnostics: CUDA events around the pieces of all_reduce()
         self._marks = []
         self._side_marks = []
-        _C.set_grad_arena_provider(self._provide)
-        if mode == "factor":
-            _C.set_sh_factor_hook(self._factor_slots)
+        self._active = 0
+
+    # The hooks that redirect the backward's outputs into the symmetric arena are installed only
+    # while this exchange is entered (`with exchange: backward(...)`): a backward issued outside
+    # the block — another rasterizer of the same size, gradient accumulation over several views —
+    # gets private buffers and a complete dL_dsh as usual.
+    def __enter__(self):
+        if self._active == 0:
+            self._C.set_grad_arena_provider(self._provide)
+            if self.mode == "factor":
+                self._C.set_sh_factor_hook(self._factor_slots)
+        self._active += 1
+        return self
+
+    def __exit__(self, *exc):
+        self._active -= 1
+        if self._active == 0:
+            self._C.set_grad_arena_provider(None)
+            self._C.set_sh_factor_hook(None)
+        return False
 
     # ---- hooks called by _C.rasterize_gaussians_backward -------------------------------------
     def _provide(self, numel, dev):
@@ -275,6 +292,7 @@ class NvlsExchange:
         return out
 
     def close(self):
+        self._active = 0
         self._C.set_grad_arena_provider(None)
         self._C.set_sh_factor_hook(None)
 
@@ -301,8 +319,8 @@ class ViewParallelRasterizer:
         self.backend = backend
         self.group = group
         self.average = average
-        if exchange not in ("nccl", "nvls"):
-            raise ValueError("exchange must be 'nccl' or 'nvls'")
+        if exchange not in ("nccl", "nvls", "none"):
+            raise ValueError("exchange must be 'nccl', 'nvls' or 'none' (per-rank gradients, no sum)")
         self.exchange = exchange
         self._nvls: Optional[NvlsExchange] = None
 
@@ -325,14 +343,16 @@ class ViewParallelRasterizer:
         dL_dpix = loss_grad(color)
         if self.average and self.world > 1:
             dL_dpix = dL_dpix / self.world     # fold the 1/G of a mean into the upstream gradient
-        grads = self.backend.rasterize_gaussians_backward(
-            bg, scene["means3D"], radii, e, scene["scales"], scene["rotations"], scale_modifier, e,
-            view, proj, cam.tanfovx, cam.tanfovy, dL_dpix, scene["shs"], sh_degree, campos, geom, R,
-            binning, img, False)
+        import contextlib
+        with (self._nvls if self._nvls is not None else contextlib.nullcontext()):
+            grads = self.backend.rasterize_gaussians_backward(
+                bg, scene["means3D"], radii, e, scene["scales"], scene["rotations"], scale_modifier, e,
+                view, proj, cam.tanfovx, cam.tanfovy, dL_dpix, scene["shs"], sh_degree, campos, geom, R,
+                binning, img, False)
         work = None
         if self.world > 1 and self._nvls is not None:
             self._nvls.all_reduce()
-        elif self.world > 1:
+        elif self.world > 1 and self.exchange != "none":
             flat, aliased = flat_leaf_gradients(grads)
             work = dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=async_op)
             if not aliased:

@@ -65,12 +65,29 @@ def check_binning_properties(m, radii, R, P, W, H):
     assert bool((n <= per_pix).all())
 
 
-def compare_with_reference(C_, sc, cam, bg, deg=3, mod=1.0, bad_frac=1e-3):
+def violations(a, b):
+    """north_star's gradient bar, per element: |a - b| <= 1e-6 + 1e-4 |b|.
+    -> (fraction of elements outside, largest error / tolerance)"""
+    a_, b_ = a.double(), b.double()
+    tol = 1e-6 + 1e-4 * b_.abs()
+    err = (a_ - b_).abs()
+    if err.numel() == 0:
+        return 0.0, 0.0
+    return (err > tol).double().mean().item(), (err / tol).max().item()
+
+
+def compare_with_reference(C_, sc, cam, bg, deg=3, mod=1.0, bad_frac=1e-3, colors_precomp=None,
+                           cov3D_precomp=None, prefiltered=False, backward=True):
+    """Same inputs through the reference's own CUDA build (oracle/_ref) and through libbgr:
+    integer buffers bit-equal, float intermediates bit-equal, image <= 1e-5, gradients at the
+    north_star bar except for the fraction of elements on which two runs of the REFERENCE itself
+    disagree (unordered float atomics; measured per call)."""
     ref = ref_backend_or_skip()
     P = sc["means3D"].shape[0]
     W, H = cam.image_width, cam.image_height
-    a_r, o_r = util.native_forward(ref, sc, cam, bg, deg, mod)
-    a_n, o_n = util.native_forward(C_, sc, cam, bg, deg, mod)
+    kw = dict(colors_precomp=colors_precomp, cov3D_precomp=cov3D_precomp, prefiltered=prefiltered)
+    a_r, o_r = util.native_forward(ref, sc, cam, bg, deg, mod, **kw)
+    a_n, o_n = util.native_forward(C_, sc, cam, bg, deg, mod, **kw)
     assert o_r[0] == o_n[0]
     g = ref.parse_geom(o_r[3], P); im = ref.parse_img(o_r[5], W, H); b = ref.parse_binning(o_r[4], o_r[0])
     m = util.bgr_intermediates(o_n, P, W, H)
@@ -80,23 +97,26 @@ def compare_with_reference(C_, sc, cam, bg, deg=3, mod=1.0, bad_frac=1e-3):
     assert torch.equal(b["point_list"], m["point_list"])
     assert torch.equal(im["ranges"][:m["ranges"].shape[0]], m["ranges"])
     assert torch.equal(im["n_contrib"], m["n_contrib"])
-    for k in ("depths", "means2D", "conic_opacity", "rgb"):
+    # (the reference leaves geom.rgb unwritten when colours are precomputed)
+    for k in ("depths", "means2D", "conic_opacity") + (("rgb",) if colors_precomp is None else ()):
         assert torch.equal(g[k][vis], m[k][vis]), k
     assert (o_r[1] - o_n[1]).abs().max().item() <= 1e-5
     assert (im["final_T"] - m["final_T"]).abs().max().item() <= 1e-5
+    if not backward:
+        return o_n
     dpix = synthetic.make_upstream_grad(H, W).cuda()
     g_r = util.native_backward(ref, a_r, o_r, dpix)
     g_r2 = util.native_backward(ref, a_r, o_r, dpix)   # the reference's own run-to-run spread
     g_n = util.native_backward(C_, a_n, o_n, dpix)
     for k, r, r2, n in zip(GRAD_NAMES, g_r, g_r2, g_n):
-        r_, r2_, n_ = r.double(), r2.double(), n.double()
-        tol = 1e-6 + 1e-4 * r_.abs()
-        spread = ((r_ - r2_).abs() > tol).double().mean().item()
-        mine = ((r_ - n_).abs() > tol).double().mean().item()
+        assert r.shape == n.shape, k
+        spread, _ = violations(r2, r)
+        mine, _ = violations(n, r)
         assert torch.isfinite(n).all(), k
         assert mine <= max(3 * spread, 2e-5), f"{k}: {mine:.2e} of elements off vs reference spread {spread:.2e}"
         ok, msg = grad_close(n.cpu().numpy(), r.cpu().numpy(), max_bad_frac=bad_frac, max_norm_err=1e-3)
         assert ok, f"{k}: {msg}"
+    return o_n
 
 
 def test_c1_100k_800x800_vs_reference_build(C_):

@@ -10,6 +10,7 @@ max-abs; gradients 1e-4 relative / 1e-6 absolute per element, with the allowance
 test_oracle_golden.py (two runs of the reference differ by more than that on ~2e-4 of the
 dL_dcov3D elements; measured numbers in DESIGN.md).
 """
+import os
 from pathlib import Path
 
 import numpy as np
@@ -76,6 +77,8 @@ def test_against_reference_golden_fixture(C_, name):
     bg = torch.tensor(g["bg"])
     args, out = util.native_forward(C_, sc, cam, bg, int(g["sh_degree"]), float(g["scale_modifier"]))
     R, color, radii, *_ = out
+    if os.environ.get("BGR_EXPECT_PAIRS"):      # child run of test_force_pairs_on_small_scenes
+        assert C_.last_forward_info()["pairs"] == 1
     m = util.bgr_intermediates(out, P, W, H)
     vis = torch.tensor(g["radii"] > 0, device="cuda")
     assert R == int(g["num_rendered"])

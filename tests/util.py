@@ -21,7 +21,7 @@ def settings_for(cam, bg, sh_degree=3, scale_modifier=1.0, device="cuda", debug=
 
 
 def native_forward(backend, scene, cam, bg, sh_degree=3, scale_modifier=1.0, colors_precomp=None,
-                   cov3D_precomp=None):
+                   cov3D_precomp=None, prefiltered=False, debug=False):
     """Calls backend.rasterize_gaussians with the reference's 19 positional arguments."""
     e = torch.Tensor([])
     dev = "cuda"
@@ -33,7 +33,7 @@ def native_forward(backend, scene, cam, bg, sh_degree=3, scale_modifier=1.0, col
     args = (bg.to(dev), scene["means3D"].to(dev), col, scene["opacities"].to(dev), sc, rot,
             scale_modifier, cov, cam.viewmatrix.to(dev), cam.projmatrix.to(dev), cam.tanfovx,
             cam.tanfovy, cam.image_height, cam.image_width, sh, sh_degree, cam.campos.to(dev),
-            False, False)
+            bool(prefiltered), bool(debug))
     return args, backend.rasterize_gaussians(*args)
 
 
