@@ -330,7 +330,7 @@ def peaks():
 NCU_RAW = "profiles/r1_d_ncu_full_raw.csv"
 _STAGE_KERNEL = {"render_backward": "render_backward_kernel", "render_forward": "render_forward_kernel",
                  "preprocess_backward": "preprocess_backward_kernel", "preprocess": "preprocess_kernel",
-                 "emit_keys": "emit_keys_kernel"}
+                 "scatter_keys": "scatter_keys_kernel", "tile_sort": "tile_sort_kernel"}
 
 
 def ncu_traffic(stage):
@@ -384,10 +384,9 @@ def roofline_report(backend, wl, steps, device):
     fp32_peak = n_sm * 128 * 2 * sm_mhz * 1e6 / 1e12  # TFLOP/s at max SM clock
     bytes_ = {
         "preprocess": 20 * P + 291 * V,
-        "scan": 8 * P,
-        "emit_keys": 20 * V + 12 * R,
-        "radix_sort": 24 * R,
-        "tile_ranges": 8 * R + 8 * tiles,
+        "tile_scan": 4 * (tiles + 2 * int(tiles ** 0.5) + 1) + 12 * tiles,   # coverage grid in, ranges + cursors out
+        "scatter_keys": 20 * V + 8 * R,                                      # rect inputs in, one 8 B key per instance out
+        "tile_sort": 12 * R,                                                 # keys in, sorted Gaussian ids out
         "clear_accumulators": 48 * P,
         "preprocess_backward": 555 * V + 284 * C,
     }
@@ -528,9 +527,9 @@ def run_sweep(args, device):
                         "visible": int((out[2] > 0).sum()), "num_rendered": R,
                         "mean_tile_list": round(R / tiles, 1), "max_tile_list": int(lens.max()),
                         "sum_n_contrib": int(m["n_contrib"].long().sum()),
-                        "key_format": {"pairs": info["pairs"], "index_bits": info["nb_idx"],
-                                       "depth_bits": info["nb_depth"], "tile_bits": info["nb_tile"],
-                                       "sort_passes": info["passes"]},
+                        "binning": {"index_bits": info["nb_idx"], "depth_bits": info["nb_depth"],
+                                    "smem_sort_capacity": info["smem_keys"],
+                                    "global_sort_path": info["global_sort_path"]},
                         "ours_ms": round(ms_ours, 4), "ours_stage_ms": {k: round(v, 4) for k, v in acc.items()},
                         "pairs_examined": st["examined"], "pairs_blended": st["blended"]}
                 if ref is not None:

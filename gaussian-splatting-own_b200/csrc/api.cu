@@ -56,11 +56,11 @@ bgr::GeomControl* pinned_control()
 
 // ---- diagnostics: per-stage CUDA-event timing (off by default) and a kernel-launch counter ------
 enum Stage {
-    ST_PREPROCESS = 0, ST_SCAN, ST_EMIT, ST_SORT, ST_RANGES, ST_RENDER_FWD, ST_ACC_CLEAR,
+    ST_PREPROCESS = 0, ST_SCAN, ST_EMIT, ST_SORT, ST_RENDER_FWD, ST_ACC_CLEAR,
     ST_RENDER_BWD, ST_PREPROCESS_BWD, ST_COUNT
 };
 const char* const kStageNames[ST_COUNT] = {
-    "preprocess", "scan", "emit_keys", "radix_sort", "tile_ranges", "render_forward",
+    "preprocess", "tile_scan", "scatter_keys", "tile_sort", "render_forward",
     "clear_accumulators", "render_backward", "preprocess_backward"};
 
 struct StageTimer {
@@ -127,7 +127,7 @@ BGR_API size_t bgr_image_bytes(int width, int height)
 {
     return bgr::image_layout((size_t)std::max(width, 0), (size_t)std::max(height, 0)).total;
 }
-BGR_API size_t bgr_binning_bytes(int R) { return bgr::binning_layout((size_t)std::max(R, 0)).total; }
+BGR_API size_t bgr_binning_bytes(int R) { return bgr::binning_layout((size_t)std::max(R, 0), true).total; }
 BGR_API size_t bgr_backward_scratch_bytes(int P)
 {
     return bgr::align_up((size_t)std::max(P, 0) * bgr::ACC_STRIDE * sizeof(float), 256);
@@ -136,18 +136,17 @@ BGR_API size_t bgr_backward_scratch_bytes(int P)
 BGR_API void bgr_geom_layout(int P, size_t* o)
 {
     const bgr::GeomLayout L = bgr::geom_layout((size_t)P);
-    o[0] = L.rec; o[1] = L.tiles; o[2] = L.offsets; o[3] = L.control;
+    o[0] = L.rec; o[1] = L.tiles;
 }
 BGR_API void bgr_image_layout(int width, int height, size_t* o)
 {
     const bgr::ImageLayout L = bgr::image_layout((size_t)width, (size_t)height);
-    o[0] = L.final_T; o[1] = L.n_contrib; o[2] = L.ranges;
+    o[0] = L.final_T; o[1] = L.n_contrib; o[2] = L.ranges; o[3] = L.control;
 }
 BGR_API void bgr_binning_layout(int R, size_t* o)
 {
-    const bgr::BinningLayout L = bgr::binning_layout((size_t)R);
-    o[0] = L.point_list; o[1] = L.keys_a; o[2] = L.keys_b; o[3] = L.vals_a; o[4] = L.vals_b;
-    o[5] = L.sort_temp;
+    const bgr::BinningLayout L = bgr::binning_layout((size_t)R, true);
+    o[0] = L.point_list; o[1] = L.keys; o[2] = L.keys_alt;
 }
 
 BGR_API int bgr_forward(const BgrForwardArgs* a, bgr_alloc_fn geom_alloc, void* geom_user,
@@ -195,16 +194,16 @@ BGR_API int bgr_forward(const BgrForwardArgs* a, bgr_alloc_fn geom_alloc, void* 
 
     GaussRec* rec = reinterpret_cast<GaussRec*>(geom + GL.rec);
     uint32_t* tiles = reinterpret_cast<uint32_t*>(geom + GL.tiles);
-    uint32_t* offsets = reinterpret_cast<uint32_t*>(geom + GL.offsets);
-    GeomControl* ctl = reinterpret_cast<GeomControl*>(geom + GL.control);
-    uint64_t* scan_state = reinterpret_cast<uint64_t*>(geom + GL.scan_state);
     float* final_T = reinterpret_cast<float*>(img + IL.final_T);
     uint32_t* n_contrib = reinterpret_cast<uint32_t*>(img + IL.n_contrib);
     uint2* ranges = reinterpret_cast<uint2*>(img + IL.ranges);
+    uint32_t* cursor = reinterpret_cast<uint32_t*>(img + IL.cursor);
+    GeomControl* ctl = reinterpret_cast<GeomControl*>(img + IL.control);
+    int* coverage = reinterpret_cast<int*>(img + IL.grid);
 
     int rc;
-    // control block (counters, depth range stored as max(~bits)/max(bits)) + scan look-back state
-    if ((rc = check_cuda(cudaMemsetAsync(ctl, 0, GL.total - GL.control, s), "memset control")))
+    // control block (counters) + coverage difference grid: adjacent, one memset
+    if ((rc = check_cuda(cudaMemsetAsync(ctl, 0, IL.total - IL.control, s), "memset control")))
         return rc;
 
     PreprocessParams pp;
@@ -216,91 +215,71 @@ BGR_API int bgr_forward(const BgrForwardArgs* a, bgr_alloc_fn geom_alloc, void* 
     pp.tan_fovx = a->tan_fovx; pp.tan_fovy = a->tan_fovy; pp.focal_x = focal_x; pp.focal_y = focal_y;
     pp.grid_x = grid_x; pp.grid_y = grid_y; pp.prefiltered = a->prefiltered;
     pp.radii = a->radii; pp.rec = rec; pp.tiles_touched = tiles; pp.control = ctl;
+    pp.coverage_grid = coverage;
     g_timer.begin(ST_PREPROCESS, s);
     launch_preprocess(pp, s);
     g_timer.end(ST_PREPROCESS, s);
     if ((rc = stage_check(debug, s, "preprocess"))) return rc;
 
     g_timer.begin(ST_SCAN, s);
-    launch_inclusive_scan(tiles, offsets, (size_t)a->P, scan_state, &ctl->scan_ticket,
-                          &ctl->num_rendered, s);
+    if (launch_tile_scan(grid_x, grid_y, coverage, ranges, cursor, ctl, s) != 0)
+        return fail(BGR_ERR_CUDA, "tile scan launch configuration rejected");
     g_timer.end(ST_SCAN, s);
-    if ((rc = stage_check(debug, s, "scan"))) return rc;
+    if ((rc = stage_check(debug, s, "tile scan"))) return rc;
 
     GeomControl* host = pinned_control();
     if (host == nullptr) return fail(BGR_ERR_CUDA, "pinned host allocation failed");
     if ((rc = check_cuda(cudaMemcpyAsync(host, ctl, sizeof(GeomControl), cudaMemcpyDeviceToHost, s),
                          "read back num_rendered")))
         return rc;
-    if ((rc = check_cuda(cudaStreamSynchronize(s), "sync after scan"))) return rc;
+    if ((rc = check_cuda(cudaStreamSynchronize(s), "sync after the tile scan"))) return rc;
 
-    // the 64-bit total decides: the u32 scan wraps at 2^32 (the reference overflows silently,
+    // the 64-bit total decides: a 32-bit count wraps at 2^32 (the reference overflows silently,
     // rasterizer_impl.cu:280-283)
     if (host->tiles_total >= (1ull << 30))
         return fail(BGR_ERR_OVERFLOW, "num_rendered = " + std::to_string(host->tiles_total) +
                                           " >= 2^30 tile instances is not supported");
     const uint32_t R = host->num_rendered;
+    if ((unsigned long long)R != host->tiles_total)
+        return fail(BGR_ERR_CUDA, "internal error: tile scan total differs from the sum of tiles_touched");
 
-    const BinningLayout BL = binning_layout((size_t)R);
-    unsigned char* bin = static_cast<unsigned char*>(binning_alloc(BL.total, binning_user));
-    if (bin == nullptr) return fail(BGR_ERR_ALLOC, "binning allocation failed");
-    uint32_t* point_list = reinterpret_cast<uint32_t*>(bin + BL.point_list);
+    // shared-memory capacity of the per-tile sort, from the longest list of this view
+    uint32_t smem_keys = std::min<uint32_t>(std::max<uint32_t>(host->max_tile_list, 128u),
+                                            TILE_SORT_MAX_SMEM_KEYS);
+    if (const char* cap = std::getenv("BGR_TILE_SORT_SMEM_KEYS")) {   // tests: force the global path
+        const long v = std::atol(cap);
+        if (v >= 64) smem_keys = std::min<uint32_t>((uint32_t)v, TILE_SORT_MAX_SMEM_KEYS);
+    }
+    smem_keys = (smem_keys + 1u) & ~1u;
+    const bool long_lists = host->max_tile_list > smem_keys;
+
+    // the alternate key array backs the general (global-memory) path of the per-tile sort, which
+    // a tile takes when its list does not fit shared memory or its depths are badly clustered
+    const BinningLayout BL = binning_layout((size_t)R, true);
+    unsigned char* bin = nullptr;
+    uint32_t* point_list = nullptr;
 
     if (R > 0) {
-        KeyFormat kf;
-        kf.depth_min = ~host->depth_min_bits;  // stored inverted so that zero-init works
-        const uint32_t depth_max = host->depth_max_bits;
-        kf.nb_idx = bits_for((uint64_t)(a->P - 1));
-        kf.nb_depth = bits_for((uint64_t)(depth_max - kf.depth_min));
-        kf.nb_tile = bits_for((uint64_t)(num_tiles - 1));
-        kf.pairs = (kf.nb_idx + kf.nb_depth + kf.nb_tile > 64 || env_flag("BGR_FORCE_PAIRS")) ? 1 : 0;
-        if (kf.pairs) {
-            kf.sort_lo = 0;
-            kf.sort_hi = kf.nb_depth + kf.nb_tile;
-            kf.tile_shift = kf.nb_depth;
-        } else {
-            kf.sort_lo = kf.nb_idx;
-            kf.sort_hi = kf.nb_idx + kf.nb_depth + kf.nb_tile;
-            kf.tile_shift = kf.nb_idx + kf.nb_depth;
-        }
-        uint64_t* keys_a = reinterpret_cast<uint64_t*>(bin + BL.keys_a);
-        uint64_t* keys_b = reinterpret_cast<uint64_t*>(bin + BL.keys_b);
-        uint32_t* vals_a = kf.pairs ? reinterpret_cast<uint32_t*>(bin + BL.vals_a) : nullptr;
-        uint32_t* vals_b = kf.pairs ? reinterpret_cast<uint32_t*>(bin + BL.vals_b) : nullptr;
-        // emit into the buffer from which an odd/even number of passes ends in keys_a
-        const int npasses = radix_sort_passes(kf.sort_lo, kf.sort_hi);
-        const int info[8] = {kf.pairs, kf.nb_idx, kf.nb_depth, kf.nb_tile, kf.sort_lo, kf.sort_hi,
-                             npasses, (int)R};
+        bin = static_cast<unsigned char*>(binning_alloc(BL.total, binning_user));
+        if (bin == nullptr) return fail(BGR_ERR_ALLOC, "binning allocation failed");
+        point_list = reinterpret_cast<uint32_t*>(bin + BL.point_list);
+        const int nb_idx = bits_for((uint64_t)(a->P - 1));
+        uint64_t* keys = reinterpret_cast<uint64_t*>(bin + BL.keys);
+        uint64_t* keys_alt = reinterpret_cast<uint64_t*>(bin + BL.keys_alt);
+        const int info[8] = {long_lists ? 1 : 0, nb_idx, 32, 0, (int)host->max_tile_list, (int)smem_keys,
+                             0, (int)R};
         std::copy(info, info + 8, g_forward_info);
-        const bool start_in_b = (npasses & 1) != 0;
-        uint64_t* k_in = start_in_b ? keys_b : keys_a;
-        uint64_t* k_alt = start_in_b ? keys_a : keys_b;
-        uint32_t* v_in = start_in_b ? vals_b : vals_a;
-        uint32_t* v_alt = start_in_b ? vals_a : vals_b;
 
         g_timer.begin(ST_EMIT, s);
-        launch_emit_keys(a->P, rec, offsets, a->radii, grid_x, grid_y, kf, k_in, v_in, s);
+        launch_scatter_keys(a->P, rec, a->radii, grid_x, grid_y, nb_idx, cursor, keys, s);
         g_timer.end(ST_EMIT, s);
-        if ((rc = stage_check(debug, s, "emit keys"))) return rc;
+        if ((rc = stage_check(debug, s, "scatter keys"))) return rc;
 
-        int in_alt = 0;
         g_timer.begin(ST_SORT, s);
-        if (radix_sort(k_in, k_alt, v_in, v_alt, (size_t)R, kf.sort_lo, kf.sort_hi,
-                       bin + BL.sort_temp, s, &in_alt, kf.tile_shift) != 0)
-            return fail(BGR_ERR_INVALID_ARG, "radix sort configuration rejected");
+        if (launch_tile_sort(num_tiles, ranges, keys, keys_alt, nb_idx, smem_keys, point_list, s) != 0)
+            return fail(BGR_ERR_CUDA, "tile sort launch configuration rejected");
         g_timer.end(ST_SORT, s);
-        if ((rc = stage_check(debug, s, "radix sort"))) return rc;
-        const uint64_t* k_sorted = in_alt ? k_alt : k_in;  // == keys_a by construction
-        const uint32_t* v_sorted = in_alt ? v_alt : v_in;
-
-        g_timer.begin(ST_RANGES, s);
-        launch_tile_ranges((size_t)R, k_sorted, v_sorted, kf, num_tiles, ranges, point_list, s);
-        g_timer.end(ST_RANGES, s);
-        if ((rc = stage_check(debug, s, "tile ranges"))) return rc;
-    } else {
-        if ((rc = check_cuda(cudaMemsetAsync(ranges, 0, (size_t)num_tiles * sizeof(uint2), s),
-                             "memset ranges")))
-            return rc;
+        if ((rc = stage_check(debug, s, "tile sort"))) return rc;
     }
 
     g_timer.begin(ST_RENDER_FWD, s);

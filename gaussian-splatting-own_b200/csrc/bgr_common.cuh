@@ -23,26 +23,26 @@ struct __align__(16) GaussRec {
 };
 static_assert(sizeof(GaussRec) == 48, "record layout");
 
-// Control block at the tail of the geometry buffer (device side).
+// Control block of one forward call (device side; lives in the image buffer next to the tile
+// counters so that ONE memset clears it together with the coverage grid).
 struct GeomControl {
-    uint32_t num_rendered;   // total tile instances (written by the scan)
-    uint32_t depth_min_bits; // max over visible Gaussians of ~float_as_uint(depth) (inverted so 0-init works)
-    uint32_t depth_max_bits; // max over visible Gaussians of float_as_uint(depth)
-    uint32_t visible;        // number of Gaussians with radii > 0
-    uint32_t scan_ticket;    // dynamic block id for the look-back scan
+    uint32_t num_rendered;           // total tile instances R (written by the tile scan)
+    uint32_t max_tile_list;          // longest per-tile list (sizes the sort's shared memory)
+    uint32_t visible;                // number of Gaussians with radii > 0
     uint32_t pad;
-    unsigned long long tiles_total;  // 64-bit sum of tiles_touched: the u32 scan total may wrap
+    unsigned long long tiles_total;  // 64-bit sum of tiles_touched: the overflow guard
+    unsigned long long pad2;
 };
 static_assert(sizeof(GeomControl) == 32, "control block layout");
 
 struct GeomLayout {
-    size_t rec, tiles, offsets, control, scan_state, total;
+    size_t rec, tiles, total;
 };
 struct ImageLayout {
-    size_t final_T, n_contrib, ranges, total;
+    size_t final_T, n_contrib, ranges, cursor, control, grid, total;
 };
 struct BinningLayout {
-    size_t point_list, keys_a, keys_b, vals_a, vals_b, sort_temp, total;
+    size_t point_list, keys, keys_alt, total;
 };
 
 // Number of kernels this library has launched (diagnostic; bumped by every launch_* wrapper).
@@ -60,21 +60,24 @@ inline GeomLayout geom_layout(size_t P)
     size_t o = 0;
     L.rec = o;        o = align_up(o + P * sizeof(GaussRec), 256);
     L.tiles = o;      o = align_up(o + P * 4, 256);
-    L.offsets = o;    o = align_up(o + P * 4, 256);
-    L.control = o;    o = align_up(o + sizeof(GeomControl), 256);
-    L.scan_state = o; o = align_up(o + ((P + SCAN_TILE - 1) / SCAN_TILE + 1) * 8, 256);
     L.total = o;
     return L;
 }
 
+// Image buffer. `grid` is the (gx+1) x (gy+1) coverage difference grid the preprocess adds the
+// four corners of every tile rectangle to; its 2-D prefix sum is the per-tile instance count.
 inline ImageLayout image_layout(size_t W, size_t H)
 {
     ImageLayout L;
-    size_t tiles = ((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+    const size_t gx = (W + TILE_X - 1) / TILE_X, gy = (H + TILE_Y - 1) / TILE_Y;
+    const size_t tiles = gx * gy;
     size_t o = 0;
     L.final_T = o;   o = align_up(o + W * H * 4, 256);
     L.n_contrib = o; o = align_up(o + W * H * 4, 256);
     L.ranges = o;    o = align_up(o + tiles * 8, 256);
+    L.cursor = o;    o = align_up(o + tiles * 4, 256);
+    L.control = o;   o = align_up(o + sizeof(GeomControl), 256);
+    L.grid = o;      o = align_up(o + (gx + 1) * (gy + 1) * 4, 256);
     L.total = o;
     return L;
 }
@@ -110,41 +113,37 @@ inline SortTempLayout sort_temp_layout(size_t n)
     return L;
 }
 
-inline BinningLayout binning_layout(size_t R)
+// Binning buffer: the sorted Gaussian-id list the render kernels read, the per-tile key buckets
+// the scatter fills, and (only when some tile list exceeds the shared-memory sort capacity) a
+// second key array the global-memory sort ping-pongs with.
+inline BinningLayout binning_layout(size_t R, bool with_alt = false)
 {
     BinningLayout L;
     size_t o = 0;
     L.point_list = o; o = align_up(o + R * 4, 256);
-    L.keys_a = o;     o = align_up(o + R * 8, 256);
-    L.keys_b = o;     o = align_up(o + R * 8, 256);
-    L.vals_a = o;     o = align_up(o + R * 4, 256);
-    L.vals_b = o;     o = align_up(o + R * 4, 256);
-    L.sort_temp = o;  o = align_up(o + sort_temp_layout(R).total, 256);
+    L.keys = o;       o = align_up(o + R * 8, 256);
+    L.keys_alt = o;   o = align_up(o + (with_alt ? R * 8 : 0), 256);
     L.total = o;
     return L;
 }
 
-// Per-Gaussian accumulators of the backward render (AoS, 12 floats):
-//   [0] dL/dmean2D.x  [1] dL/dmean2D.y  [2] dL/dconic.x  [3] dL/dconic.y
-//   [4] dL/dconic.w   [5] dL/dopacity   [6..8] dL/dcolor  [9..11] unused
+// Per-tile sort geometry (binning.cu): tiles whose list fits TILE_SORT_MAX_SMEM_KEYS keys are
+// sorted in shared memory, longer ones through global memory.
+constexpr uint32_t TILE_SORT_MAX_SMEM_KEYS = 12288;   // 2 x 96 KB of keys + 34 KB of counters
+
+// Per-Gaussian accumulators of the backward render (AoS, 12 floats), with u = G * dL/dalpha and
+// (dx, dy) = splat centre - pixel, summed over the pixels the splat was blended into:
+//   [0] sum u (cx dx + cy dy)   [1] sum u (cz dy + cy dx)   (cx, cy, cz = conic)
+//   [2] sum u dx dx   [3] sum u dx dy   [4] sum u dy dy
+//   [5] sum u (= dL/dopacity)     [6..8] dL/dcolor  [9..11] unused
 constexpr int ACC_STRIDE = 12;
 
 // ---------------------------------------------------------------------------------------------
-// Key packing chosen per call from the data (host side, after the num_rendered read-back).
-//   packed mode : key = tile << (nb_depth+nb_idx) | (depth_bits - depth_min) << nb_idx | idx
-//                 (keys only, 8 B per instance; sorted on bits [nb_idx, nb_idx+nb_depth+nb_tile))
-//   pairs mode  : key = tile << nb_depth | (depth_bits - depth_min), value = idx
-// Both orders are identical to a stable sort on the reference key tile<<32|depth_bits because
-// depth_bits - depth_min is monotone in depth_bits and ties keep emission (= index) order.
+// Instance key inside a tile bucket: depth_bits << nb_idx | index. The tile is implied by the
+// bucket, so sorting a bucket by this key is the order of a stable sort on the reference key
+// tile << 32 | depth_bits (ties in depth keep emission order = ascending index,
+// rasterizer_impl.cu:98-108). 32 depth bits + at most 31 index bits always fit 64.
 // ---------------------------------------------------------------------------------------------
-struct KeyFormat {
-    int nb_idx, nb_depth, nb_tile;
-    int pairs;            // 1 = separate u32 values
-    uint32_t depth_min;
-    int sort_lo, sort_hi; // sorted bit range
-    int tile_shift;       // key >> tile_shift = tile id
-};
-
 inline int bits_for(uint64_t max_value)
 {
     int b = 0;
@@ -163,6 +162,7 @@ struct PreprocessParams {
     const float* cam_pos; float tan_fovx, tan_fovy, focal_x, focal_y;
     int grid_x, grid_y; int prefiltered;
     int* radii; GaussRec* rec; uint32_t* tiles_touched; GeomControl* control;
+    int* coverage_grid;   // (grid_x + 1) x (grid_y + 1) difference grid, zero on entry
 };
 
 void launch_preprocess(const PreprocessParams& p, cudaStream_t s);
@@ -170,12 +170,14 @@ void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, u
                          cudaStream_t s);
 void launch_inclusive_scan(const uint32_t* in, uint32_t* out, size_t n, uint64_t* state,
                            uint32_t* ticket, uint32_t* total_out, cudaStream_t s);
-void launch_emit_keys(int P, const GaussRec* rec, const uint32_t* offsets, const int* radii,
-                      int grid_x, int grid_y, KeyFormat kf, uint64_t* keys, uint32_t* vals,
-                      cudaStream_t s);
-void launch_tile_ranges(size_t R, const uint64_t* keys_sorted, const uint32_t* vals_sorted,
-                        KeyFormat kf, uint32_t num_tiles, uint2* ranges, uint32_t* point_list,
-                        cudaStream_t s);
+int  launch_tile_scan(int grid_x, int grid_y, int* coverage_grid, uint2* ranges, uint32_t* cursor,
+                      GeomControl* control, cudaStream_t s);
+void launch_scatter_keys(int P, const GaussRec* rec, const int* radii, int grid_x, int grid_y,
+                         int nb_idx, uint32_t* cursor, uint64_t* keys, cudaStream_t s);
+// smem_keys: capacity (keys) of the shared-memory path chosen by the caller from max_tile_list;
+// keys_alt may be NULL when no tile exceeds it.
+int  launch_tile_sort(uint32_t num_tiles, const uint2* ranges, uint64_t* keys, uint64_t* keys_alt,
+                      int nb_idx, uint32_t smem_keys, uint32_t* point_list, cudaStream_t s);
 int  radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, size_t n,
                 int bit_lo, int bit_hi, void* temp, cudaStream_t s, int* result_in_b,
                  int scattered_from_bit = -1);

@@ -3,8 +3,10 @@
 // Behavioural spec: SURVEY.md App. A.2/A.3 (reference forward.cu:155-256, auxiliary.h:139-164).
 // One thread per Gaussian. Instead of the reference's eight separate scratch arrays the kernel
 // writes one 48-byte record per visible Gaussian (bgr_common.cuh: GaussRec) plus radii and
-// tiles_touched for every Gaussian, and folds the depth range (needed to shorten the sort keys)
-// and the visible count into the same pass. cov3D is not stored: the backward recomputes it.
+// tiles_touched for every Gaussian. It also adds the four corners of the Gaussian's tile rectangle
+// to a coverage difference grid, whose 2-D prefix sum (binning.cu: tile_scan_kernel) is the number
+// of instances per tile - the per-Gaussian prefix sum of the reference (rasterizer_impl.cu:277)
+// is not needed. cov3D is not stored: the backward recomputes it.
 #include <cstdio>
 #include "bgr_common.cuh"
 #include "gs_math.cuh"
@@ -59,7 +61,6 @@ __global__ void __launch_bounds__(PRE_THREADS, 4) preprocess_kernel(PreprocessPa
     const int idx = blockIdx.x * PRE_THREADS + threadIdx.x;
     uint32_t tiles = 0;
     int radius_out = 0;
-    uint32_t depth_bits = 0;
 
     if (idx < p.P) {
         const float3 p_orig = {p.means3D[3 * idx], p.means3D[3 * idx + 1], p.means3D[3 * idx + 2]};
@@ -163,7 +164,12 @@ __global__ void __launch_bounds__(PRE_THREADS, 4) preprocess_kernel(PreprocessPa
 
                     tiles = area;
                     radius_out = (int)my_radius;
-                    depth_bits = __float_as_uint(p_view.z);
+                    // coverage of [rmin, rmax): +1 / -1 at the corners, summed by tile_scan_kernel
+                    const int gw = p.grid_x + 1;
+                    atomicAdd(p.coverage_grid + rmin.y * gw + rmin.x, 1);
+                    atomicAdd(p.coverage_grid + rmin.y * gw + rmax.x, -1);
+                    atomicAdd(p.coverage_grid + rmax.y * gw + rmin.x, -1);
+                    atomicAdd(p.coverage_grid + rmax.y * gw + rmax.x, 1);
                 }
             }
         }
@@ -171,34 +177,26 @@ __global__ void __launch_bounds__(PRE_THREADS, 4) preprocess_kernel(PreprocessPa
         p.tiles_touched[idx] = tiles;
     }
 
-    // Depth range and visible count: reduced over the block first, so that the three counters
-    // (one 32-byte sector in L2) receive one set of atomics per block instead of one per warp.
-    __shared__ uint32_t s_lo[PRE_THREADS / 32], s_hi[PRE_THREADS / 32], s_cnt[PRE_THREADS / 32];
+    // Visible count and the 64-bit instance total (overflow guard): reduced over the block first,
+    // so that the counters receive one pair of atomics per block.
+    __shared__ uint32_t s_cnt[PRE_THREADS / 32];
     __shared__ uint32_t s_sum[PRE_THREADS / 32];   // <= 32 x tiles of one image: fits 32 bits
     const unsigned vis_mask = __ballot_sync(0xffffffffu, tiles != 0);
     const uint32_t wsum = __reduce_add_sync(0xffffffffu, tiles);
-    const uint32_t lo = __reduce_min_sync(0xffffffffu, tiles != 0 ? depth_bits : 0xffffffffu);
-    const uint32_t hi = __reduce_max_sync(0xffffffffu, tiles != 0 ? depth_bits : 0u);
     if ((threadIdx.x & 31) == 0) {
-        s_lo[threadIdx.x >> 5] = lo;
-        s_hi[threadIdx.x >> 5] = hi;
         s_cnt[threadIdx.x >> 5] = (uint32_t)__popc(vis_mask);
         s_sum[threadIdx.x >> 5] = wsum;
     }
     __syncthreads();
     if (threadIdx.x == 0) {
-        uint32_t blo = 0xffffffffu, bhi = 0u, bcnt = 0u;
+        uint32_t bcnt = 0u;
         unsigned long long bsum = 0ull;
 #pragma unroll
         for (int w = 0; w < PRE_THREADS / 32; ++w) {
-            blo = min(blo, s_lo[w]);
-            bhi = max(bhi, s_hi[w]);
             bcnt += s_cnt[w];
             bsum += s_sum[w];
         }
         if (bcnt != 0) {
-            atomicMax(&p.control->depth_min_bits, ~blo);
-            atomicMax(&p.control->depth_max_bits, bhi);
             atomicAdd(&p.control->visible, bcnt);
             atomicAdd(&p.control->tiles_total, bsum);
         }

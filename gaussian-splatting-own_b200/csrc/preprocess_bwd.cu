@@ -13,35 +13,40 @@ namespace bgr {
 
 namespace {
 
-constexpr int PB_THREADS = 256;
+constexpr int PB_THREADS = 128;   // 26 KB SH tile per block, ~5 blocks per SM
 
 __device__ __forceinline__ void store3(float* p, float a, float b, float c)
 {
     p[0] = a; p[1] = b; p[2] = c;
 }
 
-// kVecSH && !kFactor: dL_dsh rows are NOT written per thread (each row is 192 contiguous bytes,
-// so a warp's store instruction would touch 32 half sectors 192 bytes apart). Every lane leaves
-// its 16 basis values and dL/dRGB (zeros when culled) in a shared-memory tile and the warp then
-// writes its 32 x 48 block of products with fully coalesced 512-byte stores.
-constexpr int SH_TILE_STRIDE = 19;   // 16 basis values + dL/dRGB; odd => conflict-free rows
+// kVecSH: a Gaussian's SH row is 192 contiguous bytes, so per-thread 128-bit accesses of a warp
+// touch 32 half sectors 192 bytes apart. Rows therefore move through a shared-memory tile:
+//  * loads: the warp fetches the rows of its VISIBLE lanes cooperatively (twelve lanes per row,
+//    whole sectors, culled rows not read at all) and every lane then reads its own row from the
+//    tile, four coefficients at a time;
+//  * stores (!kFactor): every lane leaves its 16 basis values and dL/dRGB (zeros when culled) in
+//    the same tile row and the warp writes its 32 x 48 block of products with 512-byte stores.
+constexpr int SH_TILE_STRIDE = 52;   // 48 SH floats (then 16 basis values + dL/dRGB); 52 = 4 * 13
+                                     // keeps rows 16-byte aligned and quarter-warps conflict free
 
 // Per-Gaussian body. Returns the clamp-masked colour gradient dL/dRGB (zero for culled
 // Gaussians): dL/dsh[k] = basis_k(dir) * dL/dRGB is rank one, which the view-parallel path
 // exploits (kFactor: dL_dsh is NOT written here, the caller multicasts the returned factor).
 template <bool kVecSH, bool kFactor>
 __device__ __forceinline__ V3 preprocess_backward_body(const PreprocessBackwardParams& p, int idx,
-                                                       const float* s_view, const float* s_proj,
-                                                       const float* s_cam, float* tile_row)
+                                                       bool visible, const float* s_view,
+                                                       const float* s_proj, const float* s_cam,
+                                                       float* tile_row)
 {
     constexpr bool kCoop = kVecSH && !kFactor;
     const size_t i = (size_t)idx;
     const int ncoef = (p.D + 1) * (p.D + 1);
 
-    if (!(p.radii[idx] > 0)) {
+    if (!visible) {
         if (kCoop) {
 #pragma unroll
-            for (int k = 0; k < SH_TILE_STRIDE; ++k) tile_row[k] = 0.f;
+            for (int k = 0; k < 19; ++k) tile_row[k] = 0.f;
         }
         store3(p.dL_dmean2D + 3 * i, 0.f, 0.f, 0.f);
         store3(p.dL_dcolor + 3 * i, 0.f, 0.f, 0.f);
@@ -71,11 +76,18 @@ __device__ __forceinline__ V3 preprocess_backward_body(const PreprocessBackwardP
     V3 factor = v3(0.f, 0.f, 0.f);
 
     // ---- screen-space gradients accumulated by the backward render ---------------------------
+    // The render kernel leaves per-Gaussian MOMENTS of u = G * dL/dalpha about the splat centre
+    // (render_bwd.cu); the factors of backward.cu:534-552 that are constant per splat are applied
+    // here, once:  dL_dG = o * dL/dalpha,  dG/ddelx = -gdx*cx - gdy*cy,  ddelx/dx = 0.5 W, ...
     const float4* arow = reinterpret_cast<const float4*>(p.acc + i * ACC_STRIDE);
     const float4 a0 = arow[0], a1 = arow[1], a2 = arow[2];
-    const float gmx = a0.x, gmy = a0.y;               // dL/dmean2D
-    const float gcx = a0.z, gcy = a0.w, gcw = a1.x;   // dL/dconic (x, y, w)
-    const float gop = a1.y;
+    const float opac = __ldg(&p.rec[idx].q1).y;
+    const float Mx = a0.x, My = a0.y, Sxx = a0.z, Sxy = a0.w, Syy = a1.x;
+    const float mh_o = -0.5f * opac;
+    const float gmx = mh_o * Mx * (float)p.W;                             // dL/dmean2D
+    const float gmy = mh_o * My * (float)p.H;
+    const float gcx = mh_o * Sxx, gcy = mh_o * Sxy, gcw = mh_o * Syy;     // dL/dconic (x, y, w)
+    const float gop = a1.y;                                               // dL/dopacity = sum of u
     const V3 gcol = v3(a1.z, a1.w, a2.x);
     store3(p.dL_dmean2D + 3 * i, gmx, gmy, 0.f);
     store3(p.dL_dcolor + 3 * i, gcol.x, gcol.y, gcol.z);
@@ -257,26 +269,24 @@ __device__ __forceinline__ V3 preprocess_backward_body(const PreprocessBackwardP
 
         V3 dRGBdx = v3(0.f, 0.f, 0.f), dRGBdy = v3(0.f, 0.f, 0.f), dRGBdz = v3(0.f, 0.f, 0.f);
         if (kVecSH) {
-            // 48 floats in, 48 floats out, as 12 + 12 128-bit accesses, four coefficients
-            // (3 float4) at a time so that only 24 floats are live instead of 96
-            const float4* src = reinterpret_cast<const float4*>(p.shs) + i * 12;
+            // the lane's SH row is in its tile row (cooperative load in the kernel); it is consumed
+            // four coefficients (three 128-bit shared loads) at a time, then the row is reused
+            // for the basis values and dL/dRGB of the cooperative store
             float4* dst = reinterpret_cast<float4*>(p.dL_dsh) + i * 12;
-            if (kCoop) {
-#pragma unroll
-                for (int k = 0; k < 16; ++k) tile_row[k] = k < ncoef ? bas[k] : 0.f;
-                tile_row[16] = dRGB.x; tile_row[17] = dRGB.y; tile_row[18] = dRGB.z;
-            }
-            // all twelve loads are issued up front (memory-level parallelism) ...
-            float sh[48];
-#pragma unroll
-            for (int q = 0; q < 12; ++q) {
-                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (4 * (q / 3) < ncoef) v = __ldg(src + q);
-                sh[4 * q] = v.x; sh[4 * q + 1] = v.y; sh[4 * q + 2] = v.z; sh[4 * q + 3] = v.w;
-            }
-            // ... the outputs are produced and stored four coefficients at a time
+            const float4* row4 = reinterpret_cast<const float4*>(tile_row);
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
+                float sh[12];
+                if (4 * c < ncoef) {
+#pragma unroll
+                    for (int q = 0; q < 3; ++q) {
+                        const float4 v = row4[3 * c + q];
+                        sh[4 * q] = v.x; sh[4 * q + 1] = v.y; sh[4 * q + 2] = v.z; sh[4 * q + 3] = v.w;
+                    }
+                } else {
+#pragma unroll
+                    for (int q = 0; q < 12; ++q) sh[q] = 0.f;
+                }
                 float out[12];
 #pragma unroll
                 for (int kk = 0; kk < 4; ++kk) {
@@ -287,7 +297,7 @@ __device__ __forceinline__ V3 preprocess_backward_body(const PreprocessBackwardP
                         out[3 * kk] = bk * dRGB.x; out[3 * kk + 1] = bk * dRGB.y; out[3 * kk + 2] = bk * dRGB.z;
                     }
                     if (on && k > 0) {
-                        const V3 s = v3(sh[3 * k], sh[3 * k + 1], sh[3 * k + 2]);
+                        const V3 s = v3(sh[3 * kk], sh[3 * kk + 1], sh[3 * kk + 2]);
                         dRGBdx = dRGBdx + bx[k] * s;
                         dRGBdy = dRGBdy + by[k] * s;
                         dRGBdz = dRGBdz + bz[k] * s;
@@ -298,6 +308,11 @@ __device__ __forceinline__ V3 preprocess_backward_body(const PreprocessBackwardP
                     for (int q = 0; q < 3; ++q)
                         dst[3 * c + q] = make_float4(out[4 * q], out[4 * q + 1], out[4 * q + 2], out[4 * q + 3]);
                 }
+            }
+            if (kCoop) {
+#pragma unroll
+                for (int k = 0; k < 16; ++k) tile_row[k] = k < ncoef ? bas[k] : 0.f;
+                tile_row[16] = dRGB.x; tile_row[17] = dRGB.y; tile_row[18] = dRGB.z;
             }
         } else {
             const float* src = p.shs + i * p.M * 3;
@@ -414,14 +429,38 @@ __global__ void __launch_bounds__(PB_THREADS) preprocess_backward_kernel(Preproc
     __syncthreads();
 
     constexpr bool kCoop = kVecSH && !kFactor;
-    __shared__ float s_tile[kCoop ? PB_THREADS * SH_TILE_STRIDE : 1];
-    float* tile_row = kCoop ? s_tile + threadIdx.x * SH_TILE_STRIDE : nullptr;
+    __shared__ __align__(16) float s_tile[kVecSH ? PB_THREADS * SH_TILE_STRIDE : 4];
+    float* tile_row = kVecSH ? s_tile + threadIdx.x * SH_TILE_STRIDE : nullptr;
 
     const int block_first = p.begin + blockIdx.x * PB_THREADS;
     const int idx = block_first + threadIdx.x;
+    const bool visible = idx < p.end && p.radii[idx] > 0;
+    if (kVecSH) {
+        // cooperative load of the visible lanes' SH rows: float4 q of the warp's 32 x 12 block
+        // belongs to row q / 12; a row is fetched by twelve neighbouring lanes (six whole sectors)
+        const int lane = threadIdx.x & 31;
+        const unsigned vis = __ballot_sync(0xffffffffu, visible);
+        const int row0 = idx - lane;
+        const int nvec = (3 * (p.D + 1) * (p.D + 1) + 3) >> 2;   // float4 per row that hold live coefficients
+        const float4* src = reinterpret_cast<const float4*>(p.shs) + (size_t)row0 * 12;
+        float* tile = s_tile + (threadIdx.x - lane) * SH_TILE_STRIDE;
+        float4 v[12];
+#pragma unroll
+        for (int j = 0; j < 12; ++j) {
+            const int q = j * 32 + lane, r = q / 12, c = q - r * 12;
+            v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (((vis >> r) & 1u) && c < nvec) v[j] = __ldg(src + q);
+        }
+#pragma unroll
+        for (int j = 0; j < 12; ++j) {
+            const int q = j * 32 + lane, r = q / 12, c = q - r * 12;
+            if ((vis >> r) & 1u) *reinterpret_cast<float4*>(tile + r * SH_TILE_STRIDE + 4 * c) = v[j];
+        }
+        __syncwarp();
+    }
     V3 f = v3(0.f, 0.f, 0.f);
     if (idx < p.end)
-        f = preprocess_backward_body<kVecSH, kFactor>(p, idx, s_view, s_proj, s_cam, tile_row);
+        f = preprocess_backward_body<kVecSH, kFactor>(p, idx, visible, s_view, s_proj, s_cam, tile_row);
     if (kCoop) {
         // dL_dsh[r][k][c] = basis_k(r) * dL/dRGB_c(r): the warp's 32 rows, 384 float4, written in
         // twelve instructions of 512 contiguous bytes each
@@ -453,7 +492,7 @@ __global__ void __launch_bounds__(PB_THREADS) preprocess_backward_kernel(Preproc
         s_factor[3 * threadIdx.x + 1] = f.y;
         s_factor[3 * threadIdx.x + 2] = f.z;
         __syncthreads();
-        // 3*256 floats = 192 float4; begin and end are multiples of 4 (checked by the host), so
+        // 3 floats per thread; begin and end are multiples of 4 (checked by the host), so
         // the block's first float is 16-byte aligned and the valid part of the last block is a
         // whole number of float4 too
         const size_t first = (size_t)block_first * 3;                        // float index in the slot

@@ -12,8 +12,11 @@
 //    vote; otherwise the nine per-pixel gradient terms are reduced across the warp with a
 //    transposing butterfly (12 shuffles instead of 45) and leave the SM as ONE reduction per
 //    component per (warp, splat) instead of one per (pixel, splat): 9 REDs instead of up to 288;
-//  * the accumulators live in one 48-byte AoS row per Gaussian (bgr_common.cuh ACC_STRIDE) that the
-//    fused backward preprocess consumes directly.
+//  * what is accumulated per Gaussian are six moments of G * dL/dalpha about the splat centre and
+//    three colour sums (one 48-byte AoS row, bgr_common.cuh ACC_STRIDE); the per-splat constant
+//    factors of backward.cu:534-552 are applied once per Gaussian by the fused backward preprocess.
+// The per-pair arithmetic follows backward.cu:500-552 (a transcription of a mathematically fixed
+// expression, regrouped as described at the accumulation).
 #include <cstdlib>
 #include "render_common.cuh"
 
@@ -21,7 +24,8 @@ namespace bgr {
 
 namespace {
 
-__global__ void __launch_bounds__(RENDER_THREADS)
+template <int kMinBlocks>
+__global__ void __launch_bounds__(RENDER_THREADS, kMinBlocks)
 render_backward_kernel(int W, int H, const uint2* __restrict__ ranges,
                        const uint32_t* __restrict__ point_list, const GaussRec* __restrict__ rec,
                        const float* __restrict__ bg, const float* __restrict__ final_T,
@@ -72,9 +76,11 @@ render_backward_kernel(int W, int H, const uint2* __restrict__ ranges,
     if (total == 0) return;
     const int rounds = (total + RENDER_THREADS - 1) / RENDER_THREADS;
 
+    // Per-pixel state of the back-to-front recursion (backward.cu:433-437, 509-521): T before the
+    // current splat and the colour accumulated behind it. The reference keeps (last_alpha,
+    // last_color) and folds them into accum_rec lazily at the next contributing splat; folding them
+    // in right away gives the same value with four registers instead of eight.
     float accum0 = 0.f, accum1 = 0.f, accum2 = 0.f;
-    float last_alpha = 0.f;
-    float lastc0 = 0.f, lastc1 = 0.f, lastc2 = 0.f;
     float g0 = 0.f, g1 = 0.f, g2 = 0.f;
     if (inside) {
         const size_t plane = (size_t)H * W;
@@ -82,9 +88,12 @@ render_backward_kernel(int W, int H, const uint2* __restrict__ ranges,
         g1 = dL_dpix[plane + pix_id];
         g2 = dL_dpix[2 * plane + pix_id];
     }
-    const float bg_dot_dpixel = bg[0] * g0 + bg[1] * g1 + bg[2] * g2;
-    const float ddelx_dx = 0.5f * W;
-    const float ddely_dy = 0.5f * H;
+    // background term of dL/dalpha: -T_final / (1 - alpha) * (bg . dL/dpixel)  (backward.cu:529-532)
+    const float bg_term = -T_final * (bg[0] * g0 + bg[1] * g1 + bg[2] * g2);
+    // which of the nine reduced sums this lane ends up holding (see the butterfly below): lane 4k
+    // holds sum k = bit2 + 2*bit3 + 4*bit4 of the lane id, lane 2 the ninth
+    const bool red_writer = (lane & 3) == 0 || lane == 2;
+    const int red_slot = lane == 2 ? 8 : (((lane >> 2) & 1) | (((lane >> 3) & 1) << 1) | (((lane >> 4) & 1) << 2));
 
     for (int r = 0; r < rounds; ++r) {
         __syncthreads();
@@ -150,12 +159,16 @@ render_backward_kernel(int W, int H, const uint2* __restrict__ ranges,
             valid = valid && !(alpha < 1.0f / 255.0f);
             if (!__any_sync(0xffffffffu, valid)) continue;
             const float4 c = lds128(ja + 2 * PLANE_BYTES);
-            // names used by the gradient block below: b = {conic.z, opacity, r, g}, c.x = blue
-            const float4 b = make_float4(o.x, o.z, c.x, c.y);
-            const float cblue = c.z;
-
-            float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f, v4 = 0.f, v5 = 0.f, v6 = 0.f, v7 = 0.f,
-                  v8 = 0.f;
+            // What leaves the pixel are MOMENTS of u = G * dL/dalpha about the splat centre and the
+            // colour weights w = alpha * T; the factors that are constant per splat (opacity, conic,
+            // 0.5 W / 0.5 H) are applied once per Gaussian by the backward preprocess:
+            //   dL/dmean2D.x = -0.5 W o Mx,  Mx = sum u (cx dx + cy dy)     dL/dconic.x = -0.5 o Sxx
+            //   dL/dmean2D.y = -0.5 H o My,  My = sum u (cz dy + cy dx)     dL/dconic.y = -0.5 o Sxy
+            //   dL/dopacity  = S1                                           dL/dconic.w = -0.5 o Syy
+            // (backward.cu:534-552 with dL_dG = o dL/dalpha, gdx = G dx, gdy = G dy factored out).
+            // cx dx + cy dy is formed per pixel, as the reference does: for an elongated, rotated
+            // splat the two products nearly cancel and separate sums would lose the difference.
+            float u = 0.f, w = 0.f;
             if (valid) {
                 const float one_m_alpha = 1.f - alpha;
                 // 1/(1-alpha) once (MUFU.RCP + one Newton step, <= 1 ulp; 1-alpha is in [0.01, 1])
@@ -165,37 +178,21 @@ render_backward_kernel(int W, int H, const uint2* __restrict__ ranges,
                 asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rcp_oma) : "f"(one_m_alpha));
                 rcp_oma = __fmaf_rn(rcp_oma, __fmaf_rn(-one_m_alpha, rcp_oma, 1.0f), rcp_oma);
                 T = T * rcp_oma;
-                const float dchannel_dcolor = alpha * T;
-                float dL_dalpha = 0.0f;
-                const float one_m_last = 1.f - last_alpha;
-                accum0 = last_alpha * lastc0 + one_m_last * accum0;
-                lastc0 = b.z;
-                dL_dalpha += (b.z - accum0) * g0;
-                accum1 = last_alpha * lastc1 + one_m_last * accum1;
-                lastc1 = b.w;
-                dL_dalpha += (b.w - accum1) * g1;
-                accum2 = last_alpha * lastc2 + one_m_last * accum2;
-                lastc2 = cblue;
-                dL_dalpha += (cblue - accum2) * g2;
-                dL_dalpha *= T;
-                last_alpha = alpha;
-                dL_dalpha += (-T_final * rcp_oma) * bg_dot_dpixel;
-
-                const float dL_dG = b.y * dL_dalpha;
-                const float gdx = G * dx;
-                const float gdy = G * dy;
-                const float dG_ddelx = -gdx * a.z - gdy * a.w;
-                const float dG_ddely = -gdy * b.x - gdx * a.w;
-                v0 = dL_dG * dG_ddelx * ddelx_dx;
-                v1 = dL_dG * dG_ddely * ddely_dy;
-                v2 = -0.5f * gdx * dx * dL_dG;
-                v3 = -0.5f * gdx * dy * dL_dG;
-                v4 = -0.5f * gdy * dy * dL_dG;
-                v5 = G * dL_dalpha;
-                v6 = dchannel_dcolor * g0;
-                v7 = dchannel_dcolor * g1;
-                v8 = dchannel_dcolor * g2;
+                w = alpha * T;
+                const float d0 = c.x - accum0, d1 = c.y - accum1, d2 = c.z - accum2;
+                float dL_dalpha = d0 * g0;
+                dL_dalpha = __fmaf_rn(d1, g1, dL_dalpha);
+                dL_dalpha = __fmaf_rn(d2, g2, dL_dalpha);
+                accum0 = __fmaf_rn(alpha, d0, accum0);   // = alpha c + (1 - alpha) accum
+                accum1 = __fmaf_rn(alpha, d1, accum1);
+                accum2 = __fmaf_rn(alpha, d2, accum2);
+                dL_dalpha = __fmaf_rn(bg_term, rcp_oma, dL_dalpha * T);
+                u = G * dL_dalpha;
             }
+            const float ux = u * dx, uy = u * dy;
+            float v0 = u * __fmaf_rn(a.w, dy, a.z * dx), v1 = u * __fmaf_rn(a.w, dx, o.x * dy);
+            float v2 = ux * dx, v3 = ux * dy, v4 = uy * dy, v5 = u;
+            float v6 = w * g0, v7 = w * g1, v8 = w * g2;
 
             // Transposing butterfly: 8 values x 32 lanes -> each value summed over the warp.
             const bool h1 = (lane & 16) != 0;
@@ -217,14 +214,7 @@ render_backward_kernel(int W, int H, const uint2* __restrict__ ranges,
             float fin = (h4 ? v8 : sacc) + __shfl_xor_sync(0xffffffffu, h4 ? sacc : v8, 2);
             fin += __shfl_xor_sync(0xffffffffu, fin, 1);
 
-            float* row = acc + (size_t)__float_as_uint(c.w) * ACC_STRIDE;
-            // lane 4k holds value index k = bit2 + 2*bit3 + 4*bit4 of the lane id; lane 2 the ninth
-            if ((lane & 3) == 0) {
-                const int vi = ((lane >> 2) & 1) | (((lane >> 3) & 1) << 1) | (((lane >> 4) & 1) << 2);
-                atomicAdd(row + vi, fin);
-            } else if (lane == 2) {
-                atomicAdd(row + 8, fin);
-            }
+            if (red_writer) atomicAdd(acc + (size_t)__float_as_uint(c.w) * ACC_STRIDE + red_slot, fin);
         }
         }
     }
@@ -239,8 +229,14 @@ void launch_render_backward(int W, int H, const uint2* ranges, const uint32_t* p
 {
     const dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1);
     ++g_kernel_launches;
-    render_backward_kernel<<<grid, RENDER_THREADS, 0, s>>>(W, H, ranges, point_list, rec, bg, final_T,
-                                                          n_contrib, dL_dpix, acc);
+    // TEMPORARY measurement switch: 5 resident blocks per SM (51 registers, 8 bytes spilled)
+    static const bool five = [] { const char* e = std::getenv("BGR_BWD_BLOCKS"); return e && e[0] == '5'; }();
+    if (five)
+        render_backward_kernel<5><<<grid, RENDER_THREADS, 0, s>>>(W, H, ranges, point_list, rec, bg, final_T,
+                                                                 n_contrib, dL_dpix, acc);
+    else
+        render_backward_kernel<4><<<grid, RENDER_THREADS, 0, s>>>(W, H, ranges, point_list, rec, bg, final_T,
+                                                                 n_contrib, dL_dpix, acc);
 }
 
 }  // namespace bgr

@@ -407,7 +407,7 @@ def launch_count() -> int:
 def last_forward_info() -> dict:
     out = (C.c_int * 8)()
     lib().bgr_last_forward_info(out)
-    return dict(zip(("pairs", "nb_idx", "nb_depth", "nb_tile", "sort_lo", "sort_hi", "passes", "R"),
+    return dict(zip(("global_sort_path", "nb_idx", "nb_depth", "_3", "max_tile_list", "smem_keys", "_6", "R"),
                     [int(x) for x in out]))
 
 
@@ -435,22 +435,21 @@ def render_stats(fwd_out, P, W, H) -> dict:
 
 # ---- introspection helpers used by the parity tests ------------------------------------------
 def geom_layout(P):
-    o = (C.c_size_t * 4)()
+    o = (C.c_size_t * 2)()
     lib().bgr_geom_layout(int(P), o)
-    return dict(zip(("rec", "tiles_touched", "point_offsets", "control"), [int(x) for x in o]))
+    return dict(zip(("rec", "tiles_touched"), [int(x) for x in o]))
 
 
 def image_layout(W, H):
-    o = (C.c_size_t * 3)()
+    o = (C.c_size_t * 4)()
     lib().bgr_image_layout(int(W), int(H), o)
-    return dict(zip(("final_T", "n_contrib", "ranges"), [int(x) for x in o]))
+    return dict(zip(("final_T", "n_contrib", "ranges", "control"), [int(x) for x in o]))
 
 
 def binning_layout(R):
-    o = (C.c_size_t * 6)()
+    o = (C.c_size_t * 3)()
     lib().bgr_binning_layout(int(R), o)
-    return dict(zip(("point_list", "keys_a", "keys_b", "vals_a", "vals_b", "sort_temp"),
-                    [int(x) for x in o]))
+    return dict(zip(("point_list", "keys", "keys_alt"), [int(x) for x in o]))
 
 
 def radix_sort(keys: torch.Tensor, values: torch.Tensor | None, bit_lo: int, bit_hi: int):

@@ -19,7 +19,7 @@
  * absent optional input is NULL (the reference's "empty tensor => nullptr" convention,
  * rasterize_points.cu:94-111). All work is enqueued on `stream` (a cudaStream_t passed as void*).
  * bgr_forward synchronises that stream once to read back the number of rendered tile instances
- * (the reference does a blocking cudaMemcpy at rasterizer_impl.cu:281).
+ * and the longest tile list (the reference does a blocking cudaMemcpy at rasterizer_impl.cu:281).
  *
  * Every function returns BGR_OK (0) or a negative status; bgr_last_error() returns a
  * thread-local human-readable message for the last failure on the calling thread.
@@ -148,13 +148,14 @@ BGR_API size_t bgr_backward_scratch_bytes(int P);
 
 /* Introspection for the parity tests: byte offsets of the sub-arrays inside the scratch buffers.
  * geom   : [0] records (P x 48 B: x,y,conicA,conicB | conicC,opacity,r,g | b,thr,depth,clamp bits)
- *          [1] tiles_touched u32[P]   [2] point_offsets u32[P]   [3] control block
+ *          [1] tiles_touched u32[P]
  * image  : [0] final_T f32[W*H]  [1] n_contrib u32[W*H]  [2] ranges uint2[tiles]
- * binning: [0] point_list u32[R] (sorted Gaussian ids)  [1] sorted keys u64[R]
- *          [2] alternate keys u64[R]  [3] values a u32[R]  [4] values b u32[R]  [5] sort scratch */
-BGR_API void bgr_geom_layout(int P, size_t* offsets4);
-BGR_API void bgr_image_layout(int width, int height, size_t* offsets3);
-BGR_API void bgr_binning_layout(int R, size_t* offsets6);
+ *          [3] control block {u32 num_rendered, u32 longest tile list, u32 visible, ...}
+ * binning: [0] point_list u32[R] (sorted Gaussian ids)  [1] per-tile key buckets u64[R]
+ *          [2] alternate key array (present only when a tile list exceeds the shared-memory sort) */
+BGR_API void bgr_geom_layout(int P, size_t* offsets2);
+BGR_API void bgr_image_layout(int width, int height, size_t* offsets4);
+BGR_API void bgr_binning_layout(int R, size_t* offsets3);
 
 /* Sorting primitive on its own (used by tests and micro-benchmarks): stable LSD onesweep radix
  * sort of n u64 keys (optionally with u32 values) on key bits [bit_lo, bit_hi).
@@ -198,9 +199,10 @@ BGR_API int bgr_nvls_allreduce_segments_f32(void* multicast_ptr, int nseg, const
 /* ---- diagnostics (bench.py / tests; nothing here is on the product path) --------------------- */
 /* Total number of CUDA kernels this library has launched in this process. */
 BGR_API unsigned long long bgr_launch_count(void);
-/* Key format the last bgr_forward on the calling thread chose (only when num_rendered > 0):
- * [0] 1 = separate u32 values ("pairs": index + depth + tile bits exceed 64), 0 = packed keys,
- * [1] index bits [2] depth bits [3] tile bits [4],[5] sorted bit range [6] sort passes [7] R. */
+/* What the last bgr_forward on the calling thread chose for its binning (only when
+ * num_rendered > 0): [0] 1 = some tile list exceeded the shared-memory sort capacity and went
+ * through the global-memory path, [1] index bits of the bucket keys, [2] depth bits (32),
+ * [4] longest tile list, [5] shared-memory sort capacity in keys, [7] R; [3],[6] unused. */
 BGR_API void bgr_last_forward_info(int* out8);
 /* Per-stage CUDA-event timing on the launch stream: enable, run bgr_forward / bgr_backward, then
  * read the durations (ms; -1 for a stage that did not run). Stage i is named bgr_stage_name(i). */

@@ -77,8 +77,9 @@ def test_against_reference_golden_fixture(C_, name):
     bg = torch.tensor(g["bg"])
     args, out = util.native_forward(C_, sc, cam, bg, int(g["sh_degree"]), float(g["scale_modifier"]))
     R, color, radii, *_ = out
-    if os.environ.get("BGR_EXPECT_PAIRS"):      # child run of test_force_pairs_on_small_scenes
-        assert C_.last_forward_info()["pairs"] == 1
+    if os.environ.get("BGR_EXPECT_GLOBAL_SORT"):   # child run of test_global_memory_sort_path_on_small_scenes
+        info = C_.last_forward_info()
+        assert info["smem_keys"] == 96 and info["global_sort_path"] == int(info["max_tile_list"] > 96)
     m = util.bgr_intermediates(out, P, W, H)
     vis = torch.tensor(g["radii"] > 0, device="cuda")
     assert R == int(g["num_rendered"])

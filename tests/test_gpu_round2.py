@@ -1,9 +1,9 @@
 """GPU suite, part 3 (round 2): the BASELINE.json configurations and product code paths that the
 first round never reached, all against the reference's own CUDA build (oracle/_ref):
 
-  * configs[4] 4K render stress: 2M Gaussians / scale_modifier 2.0, and 10M Gaussians / degree 0,
-    which takes the "pairs" key format (index + depth + tile bits > 64: rasterizer_impl.cu:289-318
-    sorts 47 key bits there); BGR_FORCE_PAIRS on a small scene;
+  * configs[4] 4K render stress: 2M Gaussians / scale_modifier 2.0, 5M / 0.5, 10M / degree 0
+    (rasterizer_impl.cu:289-318 sorts 47 key bits there); the global-memory path of the per-tile
+    sort forced on small and mid scenes; exact depth ties;
   * configs[3] 6M Gaussians at 1080p;
   * colors_precomp / cov3D_precomp input modes (null-pointer switches rasterizer_impl.cu:321,389,411),
     SH tensors with M = 4 / 9 coefficients and a misaligned SH base (the non-vectorised kernels);
@@ -42,16 +42,15 @@ def test_c4_4k_2m_scale_modifier_2_vs_reference_build(C_):
     sc, cam = make_case(2_000_000, "4k")
     compare_with_reference(C_, sc, cam, torch.zeros(3), deg=3, mod=2.0)
     info = C_.last_forward_info()
-    assert info["pairs"] == 0 and info["nb_tile"] == 15
+    assert info["nb_idx"] == 21 and info["global_sort_path"] == 0 and info["max_tile_list"] <= info["smem_keys"]
 
 
-def test_c4_4k_10m_degree0_takes_the_pairs_path_vs_reference_build(C_):
-    """24 index bits + 26 depth bits + 15 tile bits = 65 > 64: separate value buffers."""
+def test_c4_4k_10m_degree0_vs_reference_build(C_):
+    """24 index bits + 32 depth bits per bucket key; 39M instances, lists of up to ~1 800."""
     sc, cam = make_case(10_000_000, "4k")
     compare_with_reference(C_, sc, cam, torch.tensor([0.2, 0.4, 0.6]), deg=0, mod=1.0)
     info = C_.last_forward_info()
-    assert info["pairs"] == 1, info
-    assert info["nb_idx"] == 24 and info["nb_tile"] == 15 and info["nb_idx"] + info["nb_depth"] + info["nb_tile"] > 64
+    assert info["nb_idx"] == 24 and info["nb_depth"] == 32 and info["R"] > 30_000_000, info
 
 
 def test_c4_4k_5m_scale_modifier_half_degree1(C_):
@@ -64,10 +63,11 @@ def test_c3_6m_1080p_vs_reference_build(C_):
     compare_with_reference(C_, sc, cam, torch.zeros(3))
 
 
-def test_force_pairs_on_small_scenes():
-    """BGR_FORCE_PAIRS=1 (read per call) sends every scene through the pairs key format; the
-    reference-fixture and oracle parity tests are re-run that way in a child process."""
-    env = dict(os.environ, BGR_FORCE_PAIRS="1", BGR_EXPECT_PAIRS="1")
+def test_global_memory_sort_path_on_small_scenes():
+    """BGR_TILE_SORT_SMEM_KEYS=96 (read per call) shrinks the shared-memory capacity of the per-tile
+    sort so that every longer list takes the global-memory path; the reference-fixture and oracle
+    parity tests are re-run that way in a child process."""
+    env = dict(os.environ, BGR_TILE_SORT_SMEM_KEYS="96", BGR_EXPECT_GLOBAL_SORT="1")
     r = subprocess.run([sys.executable, "-m", "pytest", str(ROOT / "tests" / "test_gpu_parity.py"), "-x", "-q",
                         "-m", "gpu", "-k", "golden or oracle", "-p", "no:cacheprovider"],
                        cwd=ROOT, env=env, capture_output=True, text=True, timeout=900)
@@ -75,11 +75,32 @@ def test_force_pairs_on_small_scenes():
     assert " passed" in r.stdout and "failed" not in r.stdout
 
 
-def test_force_pairs_mid_scene_vs_reference_build(C_, monkeypatch):
-    monkeypatch.setenv("BGR_FORCE_PAIRS", "1")
-    sc, cam = make_case(300_000, "1080p", view_seed=1)
+def test_global_memory_sort_path_mid_scene_vs_reference_build(C_, monkeypatch):
+    monkeypatch.setenv("BGR_TILE_SORT_SMEM_KEYS", "128")
+    sc, cam = make_case(1_000_000, "1080p", view_seed=1)
     compare_with_reference(C_, sc, cam, torch.zeros(3))
-    assert C_.last_forward_info()["pairs"] == 1
+    info = C_.last_forward_info()
+    assert info["global_sort_path"] == 1 and info["max_tile_list"] > 128
+
+
+def test_exact_depth_ties_keep_index_order_vs_reference_build(C_):
+    """Gaussians with bit-identical view depth in one tile: the reference's stable sort leaves
+    them in emission (= index) order (rasterizer_impl.cu:98-108, 303-308). Here they land in their
+    bucket in atomic order, so the per-tile sort has to notice the tie and sort the index digits."""
+    P = 60_000
+    sc, cam = make_case(P, "800x800", view_seed=2, seed=12)
+    g = torch.Generator().manual_seed(5)
+    pick = torch.randint(0, 300, (P,), generator=g).cuda()          # 300 distinct centres, ~200 copies each
+    sc["means3D"] = sc["means3D"][:300][pick].contiguous()
+    sc["scales"] = (sc["scales"] * 3.0).contiguous()
+    # (hundreds of coincident splats per pixel: the reference's own atomics are noisy here, so the
+    # per-element gradient allowance is the run-to-run one only; this test is about the order)
+    o_n = compare_with_reference(C_, sc, cam, torch.tensor([0.1, 0.1, 0.1]), bad_frac=1e-2)
+    m = util.bgr_intermediates(o_n, P, cam.image_width, cam.image_height)
+    # there really are adjacent list entries with equal depth
+    pl = m["point_list"].long()
+    d = m["depths"][pl]
+    assert int((d[1:] == d[:-1]).sum()) > 1000
 
 
 # ------------------------------------------------------------------------------------------------

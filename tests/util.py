@@ -58,7 +58,6 @@ def bgr_intermediates(fwd_out, P, W, H):
         "rgb": rec[:, 6:9], "thr": rec[:, 9], "depths": rec[:, 10],
         "clampbits": rec[:, 11].contiguous().view(torch.int32),
         "tiles_touched": geom[gl["tiles_touched"]:gl["tiles_touched"] + 4 * P].view(torch.int32),
-        "point_offsets": geom[gl["point_offsets"]:gl["point_offsets"] + 4 * P].view(torch.int32),
         "final_T": img[il["final_T"]:il["final_T"] + 4 * W * H].view(torch.float32).view(H, W),
         "n_contrib": img[il["n_contrib"]:il["n_contrib"] + 4 * W * H].view(torch.int32).view(H, W),
         "ranges": img[il["ranges"]:il["ranges"] + 8 * tiles].view(torch.int32).view(tiles, 2),
