@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Benchmark of the rasterizer hot path (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference|reference-ext]
 
 One "step" = forward + backward of ONE 1920x1080 view over 3M synthetic SH-degree-3 Gaussians
 (BASELINE.json configs[2]; seeded scene of SURVEY.md §8(d)). With N > 1 ranks (torchrun) every
@@ -18,6 +18,9 @@ wrote (weak scaling: per-GPU work fixed).
           same harness. The reference has no CPU rasterizer, so the comparison
           column named by north_star is its CUDA extension on the same B200; the CPU column is
           `cpu_baseline` (the plain-C oracle port, one view of the same workload).
+  --impl reference-ext : the reference's own torch extension (its setup.py sources compiled
+          unmodified by oracle/build_ref_ext.py) - the stock pybind path, to show it agrees with
+          the shim arm above.
 
 Between timed iterations nothing is flushed explicitly: the inputs (708 MB of Gaussians) are
 far larger than the 126 MB L2, which is stated in config.l2.
@@ -49,7 +52,7 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=20)
-    ap.add_argument("--impl", choices=("ours", "reference"), default="ours")
+    ap.add_argument("--impl", choices=("ours", "reference", "reference-ext"), default="ours")
     ap.add_argument("--gaussians", type=int, default=3_000_000)
     ap.add_argument("--res", choices=("800x800", "1080p", "4k"), default="1080p")
     ap.add_argument("--mode", choices=("step", "sweep"), default="step",
@@ -133,6 +136,11 @@ def load_backend(impl):
         from diff_gaussian_rasterization import _C
         _C.lib()  # fail loudly if libbgr.so is missing: there is no fallback
         return _C
+    if impl == "reference-ext":
+        # the reference's own torch extension (its setup.py sources, pybind module), built by
+        # oracle/build_ref_ext.py: same three functions, same signatures
+        from oracle import build_ref_ext
+        return build_ref_ext.load()
     from oracle import ref_backend
     if not ref_backend.available():
         return None
@@ -578,9 +586,9 @@ def main():
     backend = load_backend(args.impl)
     if backend is None:
         if rank == 0:
-            print(json.dumps({"impl": "reference", "unavailable":
-                              "oracle/_ref/libref_rasterizer.so missing (build with `make -C oracle ref` "
-                              "where /root/reference exists)"}))
+            print(json.dumps({"impl": args.impl, "unavailable":
+                              "oracle/_ref/libref_rasterizer.so (or ref_dgr_C, for reference-ext) missing: build with "
+                              "`make -C oracle ref` / `python oracle/build_ref_ext.py` where /root/reference exists"}))
         return
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the rasterizer has no CPU path")
@@ -646,7 +654,10 @@ def main():
         if world == 1 and not args.skip_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(wl)
     else:
-        line["reference"] = ("unmodified reference CUDA kernels (oracle/_ref, nvcc sm_100a) on the same GPU; "
+        line["reference"] = (("the reference's own torch extension (the five sources of its setup.py, unmodified, "
+                              "pybind module built by oracle/build_ref_ext.py for sm_100a) on the same GPU; "
+                              if args.impl == "reference-ext" else
+                              "unmodified reference CUDA kernels (oracle/_ref, nvcc sm_100a) on the same GPU; ") +
                              "the reference has no CPU implementation of this path")
         line["cpu_baseline"] = {"value": line["value"], "unit": "views/s", "cores": 0, "kind": "reference",
                                 "sample": "not a CPU run: reference CUDA extension, same workload and harness"}

@@ -688,13 +688,11 @@ int launch_tile_sort(uint32_t num_tiles, const uint2* ranges, uint64_t* keys, ui
     const size_t smem = tile_sort_smem_bytes(smem_keys, max_bin_bits);
     ++g_kernel_launches;
     // 16 keys per thread at most: the block size follows the longest list
-    // TEMPORARY experiment switch: target keys per thread
-    static const int per_thread = [] { const char* e = getenv("BGR_TILE_SORT_KPT"); int v = e ? atoi(e) : TS_KEYS_PER_THREAD; return v < 1 ? 1 : (v > TS_KEYS_PER_THREAD ? TS_KEYS_PER_THREAD : v); }();
-    if (smem_keys <= 4 * 32 * (uint32_t)per_thread)
+    if (smem_keys <= 4 * 32 * TS_KEYS_PER_THREAD)
         tile_sort_kernel<4><<<num_tiles, 128, smem, s>>>(ranges, keys, keys_alt, nb_idx, smem_keys, max_bin_bits, point_list);
-    else if (smem_keys <= 8 * 32 * (uint32_t)per_thread)
+    else if (smem_keys <= 8 * 32 * TS_KEYS_PER_THREAD)
         tile_sort_kernel<8><<<num_tiles, 256, smem, s>>>(ranges, keys, keys_alt, nb_idx, smem_keys, max_bin_bits, point_list);
-    else if (smem_keys <= 16 * 32 * (uint32_t)per_thread)
+    else if (smem_keys <= 16 * 32 * TS_KEYS_PER_THREAD)
         tile_sort_kernel<16><<<num_tiles, 512, smem, s>>>(ranges, keys, keys_alt, nb_idx, smem_keys, max_bin_bits, point_list);
     else
         tile_sort_kernel<32><<<num_tiles, 1024, smem, s>>>(ranges, keys, keys_alt, nb_idx, smem_keys, max_bin_bits, point_list);

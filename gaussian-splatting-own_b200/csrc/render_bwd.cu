@@ -229,14 +229,10 @@ void launch_render_backward(int W, int H, const uint2* ranges, const uint32_t* p
 {
     const dim3 grid((W + TILE_X - 1) / TILE_X, (H + TILE_Y - 1) / TILE_Y, 1);
     ++g_kernel_launches;
-    // TEMPORARY measurement switch: 5 resident blocks per SM (51 registers, 8 bytes spilled)
-    static const bool five = [] { const char* e = std::getenv("BGR_BWD_BLOCKS"); return e && e[0] == '5'; }();
-    if (five)
-        render_backward_kernel<5><<<grid, RENDER_THREADS, 0, s>>>(W, H, ranges, point_list, rec, bg, final_T,
-                                                                 n_contrib, dL_dpix, acc);
-    else
-        render_backward_kernel<4><<<grid, RENDER_THREADS, 0, s>>>(W, H, ranges, point_list, rec, bg, final_T,
-                                                                 n_contrib, dL_dpix, acc);
+    // four resident blocks per SM (60 registers): five (48 registers, 8 bytes spilled) measured the
+    // same within run-to-run noise (1.18-1.30 ms either way on the 3M / 1080p view)
+    render_backward_kernel<4><<<grid, RENDER_THREADS, 0, s>>>(W, H, ranges, point_list, rec, bg, final_T,
+                                                             n_contrib, dL_dpix, acc);
 }
 
 }  // namespace bgr

@@ -175,3 +175,30 @@ def test_ctypes_structs_match_the_c_header_field_by_field(tmp_path):
         assert int(got[cname]) == C.sizeof(ct), cname
         for fname, _ in ct._fields_:
             assert int(got[f"{cname}.{fname}"]) == getattr(ct, fname).offset, f"{cname}.{fname}"
+
+
+def test_boundary_extension_builds_and_exposes_the_reference_signatures():
+    """tests/boundary/rasterize_points_bgr.cpp (the reference's pybind functions over include/bgr.h)
+    compiles as a torch extension and carries the reference's arities (ext.cpp:15-18)."""
+    import importlib.util
+    import sys
+    spec = importlib.util.spec_from_file_location("boundary_build", ROOT / "tests" / "boundary" / "build.py")
+    b = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(b)
+    out = b.build()
+    assert out.exists()
+    sys.path.insert(0, str(out.parent))
+    try:
+        import bgr_boundary
+    finally:
+        sys.path.remove(str(out.parent))
+    doc = bgr_boundary.rasterize_gaussians.__doc__
+    assert doc.count("arg") == 19 and "Tuple[int" in doc.replace("tuple[int", "Tuple[int")
+    assert bgr_boundary.rasterize_gaussians_backward.__doc__.count("arg") == 21
+    assert bgr_boundary.mark_visible.__doc__.count("arg") == 3
+    # no GPU here: the binding must refuse CPU tensors through the library's own error, not crash
+    with pytest.raises(RuntimeError):
+        bgr_boundary.rasterize_gaussians(torch.zeros(3), torch.zeros(4, 2), *([torch.Tensor([])] * 2),
+                                         torch.Tensor([]), torch.Tensor([]), 1.0, torch.Tensor([]),
+                                         torch.eye(4), torch.eye(4), 1.0, 1.0, 16, 16, torch.Tensor([]), 3,
+                                         torch.zeros(3), False, False)
