@@ -163,6 +163,9 @@ struct PreprocessParams {
     int grid_x, grid_y; int prefiltered;
     int* radii; GaussRec* rec; uint32_t* tiles_touched; GeomControl* control;
     int* coverage_grid;   // (grid_x + 1) x (grid_y + 1) difference grid, zero on entry
+    // raw-leaf entry (bgr_forward_raw): scales / rotations / opacities are pre-activation, shs is
+    // _features_dc [P,1,3] and shs_rest is _features_rest [P,M-1,3]
+    int raw; const float* shs_rest;
 };
 
 void launch_preprocess(const PreprocessParams& p, cudaStream_t s);
@@ -216,6 +219,9 @@ struct PreprocessBackwardParams {
     // Gaussian range [begin, end) handled by this launch (the whole scene unless the caller
     // pipelines the kernel against the gradient exchange chunk by chunk)
     int begin, end;
+    // raw-leaf entry (bgr_backward_raw): see PreprocessParams; dL_dsh is then [P,1,3] and
+    // dL_dsh_rest [P,M-1,3], and dL_dscale / dL_drot / dL_dopacity are w.r.t. the raw leaves
+    int raw; const float* shs_rest; float* dL_dsh_rest;
 };
 void launch_preprocess_backward(const PreprocessBackwardParams& p, cudaStream_t s);
 void launch_sh_grad_from_factors(int P, int begin, int end, int D, int M, int world,

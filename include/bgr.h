@@ -136,6 +136,32 @@ BGR_API int bgr_forward(const BgrForwardArgs* args,
 
 BGR_API int bgr_backward(const BgrBackwardArgs* args, void* stream);
 
+/* ---- extended entry: the trainer's activations fused in (new) -------------
+ * The trainer keeps RAW leaves and activates them on every step before it calls the rasterizer
+ * (scene/gaussian_model.py:95-115 via gaussian_renderer/__init__.py:53-82):
+ *     scales    = exp(_scaling)              rotations = normalize(_rotation)   (x / max(|x|, 1e-12))
+ *     opacities = sigmoid(_opacity)          shs       = cat(_features_dc, _features_rest, dim=1)
+ * each of which materialises a P-sized tensor forward and another one backward (the SH cat alone
+ * copies 192 B per Gaussian each way). These two entry points take the raw leaves and do the
+ * activations inside the preprocess kernels, and the backward returns the gradients w.r.t. the RAW
+ * leaves. The argument blocks are the same, read as follows:
+ *     scales = _scaling [P,3]   rotations = _rotation [P,4]   opacities = _opacity [P]
+ *     shs = _features_dc [P,1,3]      features_rest = _features_rest [P,M-1,3] (NULL when M == 1)
+ *     M   = coefficients per channel of the two SH leaves together (1..16)
+ *     dL_dscale / dL_drot / dL_dopacity = gradients of the raw leaves
+ *     dL_dsh = dL/d_features_dc [P,1,3]     dL_dfeatures_rest = dL/d_features_rest [P,M-1,3]
+ * colors_precomp and cov3D_precomp must be NULL (use the drop-in entry for those modes), and so must
+ * the view-parallel multicast slots. Everything else - buffers, num_rendered, the image, radii and
+ * the remaining gradients - is exactly what bgr_forward / bgr_backward produce for the activated
+ * values. */
+BGR_API int bgr_forward_raw(const BgrForwardArgs* args, const float* features_rest,
+                bgr_alloc_fn geom_alloc, void* geom_user,
+                bgr_alloc_fn binning_alloc, void* binning_user,
+                bgr_alloc_fn image_alloc, void* image_user,
+                void* stream, int* num_rendered);
+BGR_API int bgr_backward_raw(const BgrBackwardArgs* args, const float* features_rest,
+                float* dL_dfeatures_rest, void* stream);
+
 /* present[i] = 1 iff Gaussian i passes the near-plane test (auxiliary.h:139-164). */
 BGR_API int bgr_mark_visible(int P, const float* means3D, const float* viewmatrix,
                      const float* projmatrix, uint8_t* present, void* stream);
@@ -152,7 +178,7 @@ BGR_API size_t bgr_backward_scratch_bytes(int P);
  * image  : [0] final_T f32[W*H]  [1] n_contrib u32[W*H]  [2] ranges uint2[tiles]
  *          [3] control block {u32 num_rendered, u32 longest tile list, u32 visible, ...}
  * binning: [0] point_list u32[R] (sorted Gaussian ids)  [1] per-tile key buckets u64[R]
- *          [2] alternate key array (present only when a tile list exceeds the shared-memory sort) */
+ *          [2] alternate key array u64[R] (ping-pong partner of the per-tile sort's general path) */
 BGR_API void bgr_geom_layout(int P, size_t* offsets2);
 BGR_API void bgr_image_layout(int width, int height, size_t* offsets4);
 BGR_API void bgr_binning_layout(int R, size_t* offsets3);
