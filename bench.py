@@ -55,10 +55,11 @@ def parse_args():
     ap.add_argument("--impl", choices=("ours", "reference", "reference-ext"), default="ours")
     ap.add_argument("--gaussians", type=int, default=3_000_000)
     ap.add_argument("--res", choices=("800x800", "1080p", "4k"), default="1080p")
-    ap.add_argument("--mode", choices=("step", "sweep"), default="step",
+    ap.add_argument("--mode", choices=("step", "sweep", "f1"), default="step",
                     help="step: the train-step bench (default). sweep: BASELINE.json configs[4], the "
                          "forward-only 4K grid over Gaussians x SH degree x scale_modifier, both arms "
-                         "per cell, written to --out")
+                         "per cell, written to --out. f1: the trainer's activation glue + drop-in path "
+                         "against the raw-leaf entry with the activations fused (SURVEY.md 8 row f1)")
     ap.add_argument("--sweep-gaussians", default="1,2,5,10", help="millions of Gaussians per cell")
     ap.add_argument("--sweep-degrees", default="0,3")
     ap.add_argument("--sweep-mods", default="0.5,1,2")
@@ -480,6 +481,76 @@ def cpu_baseline(wl):
 
 
 # --------------------------------------------------------------------------------------------
+# f1: the step in front of the path (activations + SH cat) composed in torch vs fused in the kernels
+# --------------------------------------------------------------------------------------------
+def run_f1(args, device):
+    """One view of the bench scene through the public autograd API, three ways, CUDA-event timed:
+    composed = the trainer's glue (scene/gaussian_model.py:95-115 via gaussian_renderer/__init__.py:
+    53-82: sigmoid, exp, normalize, cat) + GaussianRasterizer, gradients to the raw leaves by torch
+    autograd; fused = RawGaussianRasterizer (bgr_forward_raw / bgr_backward_raw); glue_only = the
+    activations and their backward without any rasterizer between them."""
+    import torch.nn.functional as F
+    import diff_gaussian_rasterization as dgr
+    load_backend("ours")
+    wl = Workload(args, 0, device)
+    s, c = wl.scene, wl.cam
+    o = s["opacities"].clamp(1e-4, 1 - 1e-4)
+    raw = {"xyz": s["means3D"], "features_dc": s["shs"][:, :1, :].contiguous(),
+           "features_rest": s["shs"][:, 1:, :].contiguous(), "opacity": torch.log(o / (1 - o)),
+           "scaling": torch.log(s["scales"]), "rotation": s["rotations"] * 1.25}
+    leaves = {k: v.clone().requires_grad_(True) for k, v in raw.items()}
+    settings = dgr.GaussianRasterizationSettings(
+        image_height=wl.H, image_width=wl.W, tanfovx=c.tanfovx, tanfovy=c.tanfovy, bg=wl.bg,
+        scale_modifier=1.0, viewmatrix=wl.view, projmatrix=wl.proj, sh_degree=3, campos=wl.campos,
+        prefiltered=False, debug=False)
+    drop_in, fused_mod = dgr.GaussianRasterizer(settings), dgr.RawGaussianRasterizer(settings)
+
+    def clear():
+        for t in leaves.values():
+            t.grad = None
+
+    def activate():
+        L = leaves
+        return (torch.cat((L["features_dc"], L["features_rest"]), dim=1), torch.sigmoid(L["opacity"]),
+                torch.exp(L["scaling"]), F.normalize(L["rotation"]))
+
+    def composed():
+        clear()
+        shs, opac, scales, rots = activate()
+        m2d = torch.zeros_like(leaves["xyz"], requires_grad=True)
+        img, _ = drop_in(means3D=leaves["xyz"], means2D=m2d, opacities=opac, shs=shs, scales=scales,
+                         rotations=rots)
+        img.backward(wl.dpix)
+
+    def fused():
+        clear()
+        L = leaves
+        m2d = torch.zeros_like(L["xyz"], requires_grad=True)
+        img, _ = fused_mod(L["xyz"], m2d, L["features_dc"], L["features_rest"], L["opacity"], L["scaling"],
+                           L["rotation"])
+        img.backward(wl.dpix)
+
+    g_act = None
+
+    def glue_only():
+        nonlocal g_act
+        clear()
+        acts = activate()
+        if g_act is None:
+            g_act = [torch.ones_like(a) for a in acts]
+        torch.autograd.backward(acts, g_act)
+
+    out = {"mode": "f1", "metric": "ms per view (forward + backward to the raw leaves)",
+           "config": {"workload": f"{args.gaussians} Gaussians SH3, {args.res}, one view, inputs resident"},
+           "steps": args.steps, "warmup": args.warmup}
+    for name, fn in (("composed_ms", composed), ("fused_ms", fused), ("glue_only_ms", glue_only)):
+        out[name] = round(timed(fn, args.steps, args.warmup, 1, device) / args.steps, 4)
+    out["saving_ms"] = round(out["composed_ms"] - out["fused_ms"], 4)
+    out["speedup"] = round(out["composed_ms"] / out["fused_ms"], 3)
+    print(json.dumps(out))
+
+
+# --------------------------------------------------------------------------------------------
 # configs[4]: render-only sweep at 3840x2160 (tile-list length and sort-size stress)
 # --------------------------------------------------------------------------------------------
 def run_sweep(args, device):
@@ -603,6 +674,11 @@ def main():
         if world > 1:
             raise SystemExit("--mode sweep is a single-GPU run")
         run_sweep(args, device)
+        return
+    if args.mode == "f1":
+        if world > 1 or args.impl != "ours":
+            raise SystemExit("--mode f1 is a single-GPU run of this library")
+        run_f1(args, device)
         return
 
     wl = Workload(args, rank, device)

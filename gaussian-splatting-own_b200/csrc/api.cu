@@ -149,9 +149,11 @@ BGR_API void bgr_binning_layout(int R, size_t* o)
     o[0] = L.point_list; o[1] = L.keys; o[2] = L.keys_alt;
 }
 
-BGR_API int bgr_forward(const BgrForwardArgs* a, bgr_alloc_fn geom_alloc, void* geom_user,
-                bgr_alloc_fn binning_alloc, void* binning_user, bgr_alloc_fn image_alloc,
-                void* image_user, void* stream_v, int* num_rendered)
+// raw: the argument block holds the trainer's raw leaves (bgr_forward_raw, include/bgr.h)
+static int forward_impl(const BgrForwardArgs* a, bool raw, const float* features_rest,
+                        bgr_alloc_fn geom_alloc, void* geom_user,
+                        bgr_alloc_fn binning_alloc, void* binning_user, bgr_alloc_fn image_alloc,
+                        void* image_user, void* stream_v, int* num_rendered)
 {
     using namespace bgr;
     cudaStream_t s = static_cast<cudaStream_t>(stream_v);
@@ -179,6 +181,11 @@ BGR_API int bgr_forward(const BgrForwardArgs* a, bgr_alloc_fn geom_alloc, void* 
     if (a->shs != nullptr && a->colors_precomp == nullptr &&
         (a->D < 0 || a->D > 3 || (a->D + 1) * (a->D + 1) > a->M))
         return fail(BGR_ERR_INVALID_ARG, "SH degree does not fit the coefficient count");
+    if (raw && (a->shs == nullptr || a->colors_precomp != nullptr || a->cov3D_precomp != nullptr ||
+                a->M < 1 || a->M > 16 || (a->M > 1 && features_rest == nullptr)))
+        return fail(BGR_ERR_INVALID_ARG,
+                    "raw-leaf entry: needs _features_dc (+ _features_rest when M > 1, M <= 16), _scaling, "
+                    "_rotation, _opacity and no precomputed colours / covariance");
 
     const int grid_x = (a->width + TILE_X - 1) / TILE_X;
     const int grid_y = (a->height + TILE_Y - 1) / TILE_Y;
@@ -213,6 +220,7 @@ BGR_API int bgr_forward(const BgrForwardArgs* a, bgr_alloc_fn geom_alloc, void* 
     pp.cov3D_precomp = a->cov3D_precomp; pp.colors_precomp = a->colors_precomp;
     pp.viewmatrix = a->viewmatrix; pp.projmatrix = a->projmatrix; pp.cam_pos = a->cam_pos;
     pp.tan_fovx = a->tan_fovx; pp.tan_fovy = a->tan_fovy; pp.focal_x = focal_x; pp.focal_y = focal_y;
+    pp.raw = raw ? 1 : 0; pp.shs_rest = features_rest;
     pp.grid_x = grid_x; pp.grid_y = grid_y; pp.prefiltered = a->prefiltered;
     pp.radii = a->radii; pp.rec = rec; pp.tiles_touched = tiles; pp.control = ctl;
     pp.coverage_grid = coverage;
@@ -292,7 +300,24 @@ BGR_API int bgr_forward(const BgrForwardArgs* a, bgr_alloc_fn geom_alloc, void* 
     return BGR_OK;
 }
 
-BGR_API int bgr_backward(const BgrBackwardArgs* a, void* stream_v)
+BGR_API int bgr_forward(const BgrForwardArgs* a, bgr_alloc_fn geom_alloc, void* geom_user,
+                bgr_alloc_fn binning_alloc, void* binning_user, bgr_alloc_fn image_alloc,
+                void* image_user, void* stream_v, int* num_rendered)
+{
+    return forward_impl(a, false, nullptr, geom_alloc, geom_user, binning_alloc, binning_user, image_alloc,
+                        image_user, stream_v, num_rendered);
+}
+
+BGR_API int bgr_forward_raw(const BgrForwardArgs* a, const float* features_rest, bgr_alloc_fn geom_alloc,
+                void* geom_user, bgr_alloc_fn binning_alloc, void* binning_user,
+                bgr_alloc_fn image_alloc, void* image_user, void* stream_v, int* num_rendered)
+{
+    return forward_impl(a, true, features_rest, geom_alloc, geom_user, binning_alloc, binning_user,
+                        image_alloc, image_user, stream_v, num_rendered);
+}
+
+static int backward_impl(const BgrBackwardArgs* a, bool raw, const float* features_rest,
+                         float* dL_dfeatures_rest, void* stream_v)
 {
     using namespace bgr;
     cudaStream_t s = static_cast<cudaStream_t>(stream_v);
@@ -305,6 +330,13 @@ BGR_API int bgr_backward(const BgrBackwardArgs* a, void* stream_v)
         return fail(BGR_ERR_INVALID_ARG, "required pointer is NULL");
     if (a->R > 0 && a->binning_buffer == nullptr)
         return fail(BGR_ERR_INVALID_ARG, "binning buffer is NULL");
+    if (raw && (a->shs == nullptr || a->dL_dsh == nullptr || a->scales == nullptr || a->rotations == nullptr ||
+                a->colors_precomp != nullptr || a->cov3D_precomp != nullptr || a->M < 1 || a->M > 16 ||
+                (a->M > 1 && (features_rest == nullptr || dL_dfeatures_rest == nullptr)) ||
+                a->sh_factor_multicast != nullptr))
+        return fail(BGR_ERR_INVALID_ARG,
+                    "raw-leaf entry: needs _features_dc (+ _features_rest when M > 1, M <= 16) and their gradient "
+                    "arrays, _scaling, _rotation, no precomputed colours / covariance and no multicast slots");
     const bool debug = a->debug != 0;
 
     const GeomLayout GL = geom_layout((size_t)a->P);
@@ -366,6 +398,7 @@ BGR_API int bgr_backward(const BgrBackwardArgs* a, void* stream_v)
     pb.dL_dmean3D = a->dL_dmean3D; pb.dL_dcov3D = a->dL_dcov3D; pb.dL_dsh = a->dL_dsh;
     pb.dL_dscale = a->dL_dscale; pb.dL_drot = a->dL_drot;
     pb.factor_mc = a->sh_factor_multicast; pb.campos_mc = a->campos_multicast;
+    pb.raw = raw ? 1 : 0; pb.shs_rest = features_rest; pb.dL_dsh_rest = dL_dfeatures_rest;
     if (pb.factor_mc != nullptr) {
         if (pb.shs == nullptr || pb.campos_mc == nullptr || (a->P & 3) != 0 || (begin & 3) != 0 ||
             (end & 3) != 0 || (reinterpret_cast<uintptr_t>(pb.factor_mc) & 15) != 0)
@@ -380,6 +413,17 @@ BGR_API int bgr_backward(const BgrBackwardArgs* a, void* stream_v)
     g_timer.end(ST_PREPROCESS_BWD, s);
     if ((rc = stage_check(debug, s, "preprocess backward"))) return rc;
     return BGR_OK;
+}
+
+BGR_API int bgr_backward(const BgrBackwardArgs* a, void* stream_v)
+{
+    return backward_impl(a, false, nullptr, nullptr, stream_v);
+}
+
+BGR_API int bgr_backward_raw(const BgrBackwardArgs* a, const float* features_rest, float* dL_dfeatures_rest,
+                             void* stream_v)
+{
+    return backward_impl(a, true, features_rest, dL_dfeatures_rest, stream_v);
 }
 
 BGR_API int bgr_mark_visible(int P, const float* means3D, const float* viewmatrix,

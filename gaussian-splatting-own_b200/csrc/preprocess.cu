@@ -47,7 +47,10 @@ constexpr int PRE_THREADS = 256;
 
 // kVecSH: shs has M == 16 coefficients and a 16-byte aligned base, so a Gaussian's 48 floats are
 // fetched as twelve 128-bit loads.
-template <bool kVecSH>
+// kRaw (bgr_forward_raw): the arrays are the trainer's raw leaves; exp / normalize / sigmoid
+// (scene/gaussian_model.py:95-115, the formulas of torch's CUDA kernels) are applied as the values
+// are loaded, and coefficient 0 comes from _features_dc, the others from _features_rest.
+template <bool kVecSH, bool kRaw>
 __global__ void __launch_bounds__(PRE_THREADS, 4) preprocess_kernel(PreprocessParams p)
 {
     __shared__ float s_view[16], s_proj[16], s_cam[3];
@@ -75,6 +78,11 @@ __global__ void __launch_bounds__(PRE_THREADS, 4) preprocess_kernel(PreprocessPa
             } else {
                 q = make_float4(p.rotations[4 * (size_t)idx], p.rotations[4 * (size_t)idx + 1],
                                 p.rotations[4 * (size_t)idx + 2], p.rotations[4 * (size_t)idx + 3]);
+            }
+            if (kRaw) {
+                sc = {expf(sc.x), expf(sc.y), expf(sc.z)};
+                const float inv = 1.0f / fmaxf(sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w), 1e-12f);
+                q = make_float4(q.x * inv, q.y * inv, q.z * inv, q.w * inv);
             }
         }
         const float3 p_view = xform_4x3(p_orig, s_view);
@@ -138,6 +146,13 @@ __global__ void __launch_bounds__(PRE_THREADS, 4) preprocess_kernel(PreprocessPa
                             c = sh_to_rgb(p.D, dir, [&](int k) {
                                 return v3(sh[3 * k], sh[3 * k + 1], sh[3 * k + 2]);
                             });
+                        } else if (kRaw) {
+                            const float* dc = p.shs + (size_t)idx * 3;
+                            const float* rest = p.shs_rest + (size_t)idx * (p.M - 1) * 3 - 3;
+                            c = sh_to_rgb(p.D, dir, [&](int k) {
+                                const float* src = k == 0 ? dc : rest + 3 * k;
+                                return v3(src[0], src[1], src[2]);
+                            });
                         } else {
                             const float* src = p.shs + (size_t)idx * p.M * 3;
                             c = sh_to_rgb(p.D, dir, [&](int k) {
@@ -150,7 +165,8 @@ __global__ void __launch_bounds__(PRE_THREADS, 4) preprocess_kernel(PreprocessPa
                         rgb = {p.colors_precomp[3 * (size_t)idx], p.colors_precomp[3 * (size_t)idx + 1],
                                p.colors_precomp[3 * (size_t)idx + 2]};
                     }
-                    const float opacity = p.opacities[idx];
+                    float opacity = p.opacities[idx];
+                    if (kRaw) opacity = 1.0f / (1.0f + expf(-opacity));
                     // power < thr implies opacity * exp(power) < 1/255 (margin covers logf/expf
                     // rounding); opacity <= 0 or NaN keeps the exact per-pixel path.
                     const float thr =
@@ -221,10 +237,12 @@ void launch_preprocess(const PreprocessParams& p, cudaStream_t s)
     const int blocks = (p.P + PRE_THREADS - 1) / PRE_THREADS;
     const bool vec = p.shs != nullptr && p.M == 16 && (reinterpret_cast<uintptr_t>(p.shs) & 15) == 0;
     ++g_kernel_launches;
-    if (vec)
-        preprocess_kernel<true><<<blocks, PRE_THREADS, 0, s>>>(p);
+    if (p.raw)
+        preprocess_kernel<false, true><<<blocks, PRE_THREADS, 0, s>>>(p);
+    else if (vec)
+        preprocess_kernel<true, false><<<blocks, PRE_THREADS, 0, s>>>(p);
     else
-        preprocess_kernel<false><<<blocks, PRE_THREADS, 0, s>>>(p);
+        preprocess_kernel<false, false><<<blocks, PRE_THREADS, 0, s>>>(p);
 }
 
 void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, uint8_t* present,

@@ -33,7 +33,11 @@ constexpr int SH_TILE_STRIDE = 52;   // 48 SH floats (then 16 basis values + dL/
 // Per-Gaussian body. Returns the clamp-masked colour gradient dL/dRGB (zero for culled
 // Gaussians): dL/dsh[k] = basis_k(dir) * dL/dRGB is rank one, which the view-parallel path
 // exploits (kFactor: dL_dsh is NOT written here, the caller multicasts the returned factor).
-template <bool kVecSH, bool kFactor>
+// kRaw (bgr_backward_raw): the inputs are the trainer's raw leaves (activated here exactly as
+// the forward did) and dL_dscale / dL_drot / dL_dopacity are chained through exp / normalize /
+// sigmoid; the SH row and the SH gradients move through the tile as with kVecSH, the kernel splits
+// them between the _features_dc and _features_rest layouts.
+template <bool kVecSH, bool kFactor, bool kRaw>
 __device__ __forceinline__ V3 preprocess_backward_body(const PreprocessBackwardParams& p, int idx,
                                                        bool visible, const float* s_view,
                                                        const float* s_proj, const float* s_cam,
@@ -48,6 +52,7 @@ __device__ __forceinline__ V3 preprocess_backward_body(const PreprocessBackwardP
 #pragma unroll
             for (int k = 0; k < 19; ++k) tile_row[k] = 0.f;
         }
+        if (kRaw) store3(p.dL_dsh + 3 * i, 0.f, 0.f, 0.f);
         store3(p.dL_dmean2D + 3 * i, 0.f, 0.f, 0.f);
         store3(p.dL_dcolor + 3 * i, 0.f, 0.f, 0.f);
         p.dL_dopacity[i] = 0.f;
@@ -91,7 +96,8 @@ __device__ __forceinline__ V3 preprocess_backward_body(const PreprocessBackwardP
     const V3 gcol = v3(a1.z, a1.w, a2.x);
     store3(p.dL_dmean2D + 3 * i, gmx, gmy, 0.f);
     store3(p.dL_dcolor + 3 * i, gcol.x, gcol.y, gcol.z);
-    p.dL_dopacity[i] = gop;
+    // raw leaf: d sigmoid(x) = o (1 - o)
+    p.dL_dopacity[i] = kRaw ? gop * ((1.0f - opac) * opac) : gop;
 
     const float3 mean = {p.means3D[3 * i], p.means3D[3 * i + 1], p.means3D[3 * i + 2]};
 
@@ -103,6 +109,12 @@ __device__ __forceinline__ V3 preprocess_backward_body(const PreprocessBackwardP
         sc = float3{p.scales[3 * i], p.scales[3 * i + 1], p.scales[3 * i + 2]};
         q = float4{p.rotations[4 * i], p.rotations[4 * i + 1], p.rotations[4 * i + 2],
                    p.rotations[4 * i + 3]};
+    }
+    float q_inv_norm = 1.0f;
+    if (kRaw) {
+        sc = float3{expf(sc.x), expf(sc.y), expf(sc.z)};
+        q_inv_norm = 1.0f / fmaxf(sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w), 1e-12f);
+        q = float4{q.x * q_inv_norm, q.y * q_inv_norm, q.z * q_inv_norm, q.w * q_inv_norm};
     }
     if (p.cov3D_precomp != nullptr) {
 #pragma unroll
@@ -314,6 +326,7 @@ __device__ __forceinline__ V3 preprocess_backward_body(const PreprocessBackwardP
                 for (int k = 0; k < 16; ++k) tile_row[k] = k < ncoef ? bas[k] : 0.f;
                 tile_row[16] = dRGB.x; tile_row[17] = dRGB.y; tile_row[18] = dRGB.z;
             }
+            if (kRaw) store3(p.dL_dsh + 3 * i, bas[0] * dRGB.x, bas[0] * dRGB.y, bas[0] * dRGB.z);
         } else {
             const float* src = p.shs + i * p.M * 3;
             float* dst = p.dL_dsh + i * p.M * 3;
@@ -383,6 +396,9 @@ __device__ __forceinline__ V3 preprocess_backward_body(const PreprocessBackwardP
 #pragma unroll
             for (int bb = 0; bb < 3; ++bb) Gm[aa][bb] = s[aa] * dM[aa][bb];
         }
+        if (kRaw) {   // d exp(x) = exp(x)
+            dscale[0] *= sc.x; dscale[1] *= sc.y; dscale[2] *= sc.z;
+        }
         store3(p.dL_dscale + 3 * i, dscale[0], dscale[1], dscale[2]);
 
         float4 dq;
@@ -390,6 +406,11 @@ __device__ __forceinline__ V3 preprocess_backward_body(const PreprocessBackwardP
         dq.y = 2 * y * (Gm[1][0] + Gm[0][1]) + 2 * z * (Gm[2][0] + Gm[0][2]) + 2 * r * (Gm[1][2] - Gm[2][1]) - 4 * x * (Gm[2][2] + Gm[1][1]);
         dq.z = 2 * x * (Gm[1][0] + Gm[0][1]) + 2 * r * (Gm[2][0] - Gm[0][2]) + 2 * z * (Gm[1][2] + Gm[2][1]) - 4 * y * (Gm[2][2] + Gm[0][0]);
         dq.w = 2 * r * (Gm[0][1] - Gm[1][0]) + 2 * x * (Gm[2][0] + Gm[0][2]) + 2 * y * (Gm[1][2] + Gm[2][1]) - 4 * z * (Gm[1][1] + Gm[0][0]);
+        if (kRaw) {   // through q / |q|: (g - q (q . g)) / |q| with q already unit length
+            const float qg = r * dq.x + x * dq.y + y * dq.z + z * dq.w;
+            dq.x = (dq.x - r * qg) * q_inv_norm; dq.y = (dq.y - x * qg) * q_inv_norm;
+            dq.z = (dq.z - y * qg) * q_inv_norm; dq.w = (dq.w - z * qg) * q_inv_norm;
+        }
         if ((reinterpret_cast<uintptr_t>(p.dL_drot) & 15) == 0) {
             reinterpret_cast<float4*>(p.dL_drot)[i] = dq;
         } else {
@@ -416,9 +437,10 @@ __device__ __forceinline__ void mm_st4(float4* p, float4 v)
 // one store, the NVSwitch replicates it) into slot `dp_rank` of a symmetric buffer on every GPU —
 // the all-gather is done by the kernel that produces the data, while it is still computing. Each
 // rank later rebuilds sum_v basis(dir_v) x factor_v locally (sh_grad_from_factors_kernel).
-template <bool kVecSH, bool kFactor>
+template <bool kVecSH, bool kFactor, bool kRaw>
 __global__ void __launch_bounds__(PB_THREADS) preprocess_backward_kernel(PreprocessBackwardParams p)
 {
+    static_assert(!kRaw || (kVecSH && !kFactor), "the raw-leaf path uses the tile and writes its SH gradients");
     __shared__ float s_view[16], s_proj[16], s_cam[3];
     __shared__ __align__(16) float s_factor[kFactor ? 3 * PB_THREADS : 4];
     if (threadIdx.x < 16) {
@@ -435,7 +457,28 @@ __global__ void __launch_bounds__(PB_THREADS) preprocess_backward_kernel(Preproc
     const int block_first = p.begin + blockIdx.x * PB_THREADS;
     const int idx = block_first + threadIdx.x;
     const bool visible = idx < p.end && p.radii[idx] > 0;
-    if (kVecSH) {
+    // raw leaves: the warp's 32 rows of _features_rest are one contiguous block of 32 x rw floats
+    // (rw = 3 (M - 1), any alignment); element e of it belongs to row e / rw. raw_div = ceil(2^16 /
+    // rw) turns the division into a multiply for e < 32 x 48.
+    const int rw = kRaw ? 3 * (p.M - 1) : 0;
+    const uint32_t raw_div = kRaw && rw > 0 ? (65536u + rw - 1) / rw : 0u;
+    if (kRaw) {
+        const int lane = threadIdx.x & 31;
+        const unsigned vis = __ballot_sync(0xffffffffu, visible);
+        const int row0 = idx - lane;
+        const int live = 3 * ((p.D + 1) * (p.D + 1) - 1);     // floats of a rest row that are used
+        float* tile = s_tile + (threadIdx.x - lane) * SH_TILE_STRIDE;
+        if (visible) {
+            const float* dc = p.shs + 3 * (size_t)idx;
+            tile_row[0] = dc[0]; tile_row[1] = dc[1]; tile_row[2] = dc[2];
+        }
+        const float* src = p.shs_rest + (size_t)row0 * rw;
+        for (int e = lane; e < 32 * rw; e += 32) {
+            const int r = (int)(((uint32_t)e * raw_div) >> 16), c = e - r * rw;
+            if (((vis >> r) & 1u) && c < live) tile[r * SH_TILE_STRIDE + 3 + c] = __ldg(src + e);
+        }
+        __syncwarp();
+    } else if (kVecSH) {
         // cooperative load of the visible lanes' SH rows: float4 q of the warp's 32 x 12 block
         // belongs to row q / 12; a row is fetched by twelve neighbouring lanes (six whole sectors)
         const int lane = threadIdx.x & 31;
@@ -460,8 +503,23 @@ __global__ void __launch_bounds__(PB_THREADS) preprocess_backward_kernel(Preproc
     }
     V3 f = v3(0.f, 0.f, 0.f);
     if (idx < p.end)
-        f = preprocess_backward_body<kVecSH, kFactor>(p, idx, visible, s_view, s_proj, s_cam, tile_row);
-    if (kCoop) {
+        f = preprocess_backward_body<kVecSH, kFactor, kRaw>(p, idx, visible, s_view, s_proj, s_cam, tile_row);
+    if (kRaw) {
+        // dL/d_features_rest[r][k-1][c] = basis_k(r) * dL/dRGB_c(r), k >= 1: the warp's block of
+        // 32 x rw floats, 128 contiguous bytes per store instruction
+        __syncwarp();
+        const int lane = threadIdx.x & 31;
+        const int row0 = idx - lane;
+        const int rows = min(32, p.end - row0);
+        const float* tile = s_tile + (threadIdx.x - lane) * SH_TILE_STRIDE;
+        float* dst = p.dL_dsh_rest + (size_t)row0 * rw;
+        for (int e = lane; e < rows * rw; e += 32) {
+            const int r = (int)(((uint32_t)e * raw_div) >> 16), c = e - r * rw;
+            const int k = (c * 21846) >> 16;                  // c / 3 for c < 48
+            const float* row = tile + r * SH_TILE_STRIDE;
+            dst[e] = row[k + 1] * row[16 + c - 3 * k];
+        }
+    } else if (kCoop) {
         // dL_dsh[r][k][c] = basis_k(r) * dL/dRGB_c(r): the warp's 32 rows, 384 float4, written in
         // twelve instructions of 512 contiguous bytes each
         __syncwarp();
@@ -625,15 +683,17 @@ void launch_preprocess_backward(const PreprocessBackwardParams& p, cudaStream_t 
                      (reinterpret_cast<uintptr_t>(p.shs) & 15) == 0 &&
                      (factor || (reinterpret_cast<uintptr_t>(p.dL_dsh) & 15) == 0);
     ++g_kernel_launches;
-    if (factor) {
+    if (p.raw) {
+        preprocess_backward_kernel<true, false, true><<<blocks, PB_THREADS, 0, s>>>(p);
+    } else if (factor) {
         if (vec)
-            preprocess_backward_kernel<true, true><<<blocks, PB_THREADS, 0, s>>>(p);
+            preprocess_backward_kernel<true, true, false><<<blocks, PB_THREADS, 0, s>>>(p);
         else
-            preprocess_backward_kernel<false, true><<<blocks, PB_THREADS, 0, s>>>(p);
+            preprocess_backward_kernel<false, true, false><<<blocks, PB_THREADS, 0, s>>>(p);
     } else if (vec) {
-        preprocess_backward_kernel<true, false><<<blocks, PB_THREADS, 0, s>>>(p);
+        preprocess_backward_kernel<true, false, false><<<blocks, PB_THREADS, 0, s>>>(p);
     } else {
-        preprocess_backward_kernel<false, false><<<blocks, PB_THREADS, 0, s>>>(p);
+        preprocess_backward_kernel<false, false, false><<<blocks, PB_THREADS, 0, s>>>(p);
     }
 }
 

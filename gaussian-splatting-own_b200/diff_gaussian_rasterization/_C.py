@@ -80,6 +80,11 @@ def lib() -> C.CDLL:
                               _ALLOC_FN, C.c_void_p, C.c_void_p, C.POINTER(C.c_int)]
     L.bgr_backward.restype = C.c_int
     L.bgr_backward.argtypes = [C.POINTER(_BackwardArgs), C.c_void_p]
+    L.bgr_forward_raw.restype = C.c_int
+    L.bgr_forward_raw.argtypes = [C.POINTER(_ForwardArgs), C.c_void_p, _ALLOC_FN, C.c_void_p, _ALLOC_FN,
+                                  C.c_void_p, _ALLOC_FN, C.c_void_p, C.c_void_p, C.POINTER(C.c_int)]
+    L.bgr_backward_raw.restype = C.c_int
+    L.bgr_backward_raw.argtypes = [C.POINTER(_BackwardArgs), C.c_void_p, C.c_void_p, C.c_void_p]
     L.bgr_mark_visible.restype = C.c_int
     L.bgr_mark_visible.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                    C.c_void_p]
@@ -300,6 +305,94 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
             scratch.record_stream(torch.cuda.current_stream(dev))
     return (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
             dL_drotations)
+
+
+# ---- extended entry: raw leaves in, raw-leaf gradients out ---------------
+def rasterize_gaussians_raw(background, xyz, opacity_raw, scaling_raw, rotation_raw, scale_modifier,
+                            viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width,
+                            features_dc, features_rest, degree, campos, prefiltered, debug):
+    """Forward over the trainer's RAW leaves (scene/gaussian_model.py:95-115): `_opacity` (P,1)
+    logits, `_scaling` (P,3) log-scales, `_rotation` (P,4) unnormalised, `_features_dc` (P,1,3) and
+    `_features_rest` (P,M-1,3); sigmoid / exp / normalize / cat happen inside the preprocess kernel
+    (bgr_forward_raw). Same return tuple as rasterize_gaussians."""
+    if xyz.dim() != 2 or xyz.size(1) != 3:
+        raise RuntimeError("xyz must have dimensions (num_points, 3)")
+    if not xyz.is_cuda:
+        raise RuntimeError("the rasterizer is CUDA-only: xyz must be a CUDA tensor")
+    L = lib()
+    dev = xyz.device
+    P, H, W = int(xyz.size(0)), int(image_height), int(image_width)
+    geom, binning, img = _Grower(dev), _Grower(dev), _Grower(dev)
+    with torch.cuda.device(dev):
+        out_color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+        radii = torch.empty((P,), dtype=torch.int32, device=dev)
+        if P == 0:
+            out_color.zero_()
+            return 0, out_color, radii, geom.tensor, binning.tensor, img.tensor
+        if features_dc.dim() != 3 or features_dc.size(1) != 1 or features_rest.dim() != 3:
+            raise RuntimeError("features_dc must be (P,1,3) and features_rest (P,M-1,3)")
+        M = 1 + int(features_rest.size(1))
+        keep = [_f32c(t, dev) for t in (background, xyz, features_dc, features_rest, opacity_raw,
+                                        scaling_raw, rotation_raw, viewmatrix, projmatrix, campos)]
+        bg_, xyz_, dc_, rest_, op_, sc_, rot_, view_, proj_, cam_ = keep
+        a = _ForwardArgs(
+            P=P, D=int(degree), M=M, width=W, height=H, background=_ptr(bg_), means3D=_ptr(xyz_),
+            shs=_ptr(dc_), colors_precomp=None, opacities=_ptr(op_), scales=_ptr(sc_),
+            scale_modifier=float(scale_modifier), rotations=_ptr(rot_), cov3D_precomp=None,
+            viewmatrix=_ptr(view_), projmatrix=_ptr(proj_), cam_pos=_ptr(cam_),
+            tan_fovx=float(tan_fovx), tan_fovy=float(tan_fovy), prefiltered=int(bool(prefiltered)),
+            debug=int(bool(debug)), out_color=out_color.data_ptr(), radii=radii.data_ptr())
+        rendered = C.c_int(0)
+        rc = L.bgr_forward_raw(C.byref(a), _ptr(rest_), geom.cb, None, binning.cb, None, img.cb, None,
+                               _stream(dev), C.byref(rendered))
+        _check(rc)
+    return int(rendered.value), out_color, radii, geom.tensor, binning.tensor, img.tensor
+
+
+def rasterize_gaussians_raw_backward(background, xyz, radii, scaling_raw, rotation_raw, scale_modifier,
+                                     viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color,
+                                     features_dc, features_rest, degree, campos, geomBuffer, R,
+                                     binningBuffer, imageBuffer, debug):
+    """-> (dL_dmeans2D (P,3), dL_dopacity_raw (P,1), dL_dxyz (P,3), dL_dfeatures_dc (P,1,3),
+    dL_dfeatures_rest (P,M-1,3), dL_dscaling_raw (P,3), dL_drotation_raw (P,4)): gradients of the
+    raw leaves, the activations' derivatives applied inside the backward preprocess kernel."""
+    L = lib()
+    dev = xyz.device
+    P = int(xyz.size(0))
+    H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
+    M = 1 + int(features_rest.size(1))
+    with torch.cuda.device(dev):
+        # one arena; [colors 3 | cov3D 6] are by-products nobody reads on this path
+        widths = (3, 3, 6, 3, 1, 3, 4, 3, 3 * (M - 1))
+        arena = torch.empty((P * sum(widths),), dtype=torch.float32, device=dev)
+        parts, o = [], 0
+        for w in widths:
+            parts.append(arena[o:o + P * w])
+            o += P * w
+        dL_dmeans2D, dL_dcolors, dL_dcov3D = parts[0].view(P, 3), parts[1].view(P, 3), parts[2].view(P, 6)
+        dL_dxyz, dL_dopacity = parts[3].view(P, 3), parts[4].view(P, 1)
+        dL_dscaling, dL_drotation = parts[5].view(P, 3), parts[6].view(P, 4)
+        dL_ddc, dL_drest = parts[7].view(P, 1, 3), parts[8].view(P, M - 1, 3)
+        if P != 0:
+            scratch = torch.empty((L.bgr_backward_scratch_bytes(P),), dtype=torch.uint8, device=dev)
+            keep = [_f32c(t, dev) for t in (background, xyz, features_dc, features_rest, scaling_raw,
+                                            rotation_raw, viewmatrix, projmatrix, campos, dL_dout_color)]
+            bg_, xyz_, dc_, rest_, sc_, rot_, view_, proj_, cam_, dpix_ = keep
+            radii_ = radii.contiguous()
+            a = _BackwardArgs(
+                P=P, D=int(degree), M=M, R=int(R), width=W, height=H, background=_ptr(bg_),
+                means3D=_ptr(xyz_), shs=_ptr(dc_), colors_precomp=None, scales=_ptr(sc_),
+                scale_modifier=float(scale_modifier), rotations=_ptr(rot_), cov3D_precomp=None,
+                viewmatrix=_ptr(view_), projmatrix=_ptr(proj_), cam_pos=_ptr(cam_),
+                tan_fovx=float(tan_fovx), tan_fovy=float(tan_fovy), radii=radii_.data_ptr(),
+                geom_buffer=_ptr(geomBuffer), binning_buffer=_ptr(binningBuffer),
+                image_buffer=_ptr(imageBuffer), dL_dpix=_ptr(dpix_), scratch=scratch.data_ptr(),
+                dL_dmean2D=_ptr(dL_dmeans2D), dL_dcolor=_ptr(dL_dcolors), dL_dopacity=_ptr(dL_dopacity),
+                dL_dmean3D=_ptr(dL_dxyz), dL_dcov3D=_ptr(dL_dcov3D), dL_dsh=_ptr(dL_ddc),
+                dL_dscale=_ptr(dL_dscaling), dL_drot=_ptr(dL_drotation), debug=int(bool(debug)))
+            _check(L.bgr_backward_raw(C.byref(a), _ptr(rest_), _ptr(dL_drest), _stream(dev)))
+            scratch.record_stream(torch.cuda.current_stream(dev))
+    return dL_dmeans2D, dL_dopacity, dL_dxyz, dL_ddc, dL_drest, dL_dscaling, dL_drotation
 
 
 def mark_visible(means3D, viewmatrix, projmatrix):

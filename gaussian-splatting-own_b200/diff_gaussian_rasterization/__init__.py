@@ -26,6 +26,7 @@ from . import _C
 __all__ = [
     "GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians",
     "_RasterizeGaussians", "cpu_deep_copy_tuple", "make_rasterize_function",
+    "RawGaussianRasterizer", "_RasterizeGaussiansRaw",
 ]
 
 
@@ -153,3 +154,58 @@ class GaussianRasterizer(nn.Module):
         cov3D_precomp = _absent() if cov3D_precomp is None else cov3D_precomp
         return self._rasterize(means3D, means2D, shs, colors_precomp, opacities, scales, rotations,
                                cov3D_precomp, self.raster_settings)
+
+
+# ---- extended entry beside the drop-in one ----------------------------------
+class _RasterizeGaussiansRaw(torch.autograd.Function):
+    """The trainer's RAW leaves in, gradients of the raw leaves out: what
+    gaussian_renderer/__init__.py:53-82 + scene/gaussian_model.py:95-115 compute with four
+    elementwise kernels and a 192-byte-per-Gaussian SH concatenation in front of the rasterizer
+    (and their backward behind it) happens inside the preprocess kernels."""
+
+    @staticmethod
+    def forward(ctx, xyz, means2D, features_dc, features_rest, opacity_raw, scaling_raw, rotation_raw,
+                raster_settings):
+        rs = raster_settings
+        args = (rs.bg, xyz, opacity_raw, scaling_raw, rotation_raw, rs.scale_modifier, rs.viewmatrix,
+                rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, features_dc,
+                features_rest, rs.sh_degree, rs.campos, rs.prefiltered, rs.debug)
+        num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer = _call_native(
+            _C.rasterize_gaussians_raw, args, rs.debug, "snapshot_fw.dump", "forward")
+        ctx.raster_settings = rs
+        ctx.num_rendered = num_rendered
+        ctx.save_for_backward(xyz, scaling_raw, rotation_raw, radii, features_dc, features_rest,
+                              geomBuffer, binningBuffer, imgBuffer)
+        return color, radii
+
+    @staticmethod
+    def backward(ctx, grad_out_color, _grad_radii):
+        rs = ctx.raster_settings
+        (xyz, scaling_raw, rotation_raw, radii, features_dc, features_rest, geomBuffer, binningBuffer,
+         imgBuffer) = ctx.saved_tensors
+        args = (rs.bg, xyz, radii, scaling_raw, rotation_raw, rs.scale_modifier, rs.viewmatrix,
+                rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_out_color, features_dc, features_rest,
+                rs.sh_degree, rs.campos, geomBuffer, ctx.num_rendered, binningBuffer, imgBuffer, rs.debug)
+        (g_means2D, g_opacity, g_xyz, g_dc, g_rest, g_scaling, g_rotation) = _call_native(
+            _C.rasterize_gaussians_raw_backward, args, rs.debug, "snapshot_bw.dump", "backward")
+        return g_xyz, g_means2D, g_dc, g_rest, g_opacity, g_scaling, g_rotation, None
+
+
+class RawGaussianRasterizer(nn.Module):
+    """``GaussianRasterizer`` for callers that hold the trainer's parameters: pass `_xyz`,
+    `_features_dc`, `_features_rest`, `_opacity`, `_scaling`, `_rotation` as they are stored
+    (scene/gaussian_model.py:47-52) instead of their activated views. Returns (color, radii) like
+    the drop-in module; `means2D` receives the screen-space gradient the densifier reads."""
+
+    def __init__(self, raster_settings):
+        super().__init__()
+        self.raster_settings = raster_settings
+
+    def markVisible(self, positions):
+        with torch.no_grad():
+            rs = self.raster_settings
+            return _C.mark_visible(positions, rs.viewmatrix, rs.projmatrix)
+
+    def forward(self, xyz, means2D, features_dc, features_rest, opacity_raw, scaling_raw, rotation_raw):
+        return _RasterizeGaussiansRaw.apply(xyz, means2D, features_dc, features_rest, opacity_raw,
+                                            scaling_raw, rotation_raw, self.raster_settings)

@@ -144,6 +144,8 @@ class NvlsExchange:
         self.profile = False     # diagnostics: CUDA events around the pieces of all_reduce()
         self._marks = []
         self._side_marks = []
+        self._pipe_marks = []    # profile, pipelined mode: per range (ready, barrier, sum, rebuild0, rebuild1)
+        self._pipe_calls = []    # ... per call: (marks of its ranges, end event)
         self._active = 0
 
     # The hooks that redirect the backward's outputs into the symmetric arena are installed only
@@ -187,6 +189,10 @@ class NvlsExchange:
         P, n = self.P, p1 - p0
         cur = torch.cuda.current_stream(self.device)
         self._make_streams()
+        ev = (lambda: torch.cuda.Event(enable_timing=True)) if self.profile else (lambda: None)
+        e_ready, e_bar, e_sum, e_rb0, e_rb1 = ev(), ev(), ev(), ev(), ev()
+        if self.profile:
+            e_ready.record(cur)
         self._side.wait_stream(cur)
         leaf0 = P * self.NON_LEAF_FLOATS
         base = self.buf.data_ptr()
@@ -194,17 +200,26 @@ class NvlsExchange:
             self.hdl.barrier(channel=0)   # every rank has produced (and multicast) this range
             ready = torch.cuda.Event()
             ready.record()
+            if self.profile:
+                e_bar.record()
             # the fabric-bound kernel first (one CTA per SM, high-priority stream): the HBM-bound
             # rebuild and the next range's preprocess fill the rest of the machine around it
             segs = [(leaf0 + 3 * p0, 3 * n), (leaf0 + 3 * P + p0, n), (leaf0 + 4 * P + 3 * p0, 3 * n),
                     (leaf0 + 7 * P + 4 * p0, 4 * n)]   # means3D | opacity | scales | rotations rows
             self._C.nvls_allreduce_segments(self.hdl.multicast_ptr, segs, self.rank, self.world,
                                             self.device, self.max_blocks)
+            if self.profile:
+                e_sum.record()
         self._side2.wait_event(ready)
         with torch.cuda.stream(self._side2):
+            if self.profile:
+                e_rb0.record()
             self._C.sh_grad_from_factors_range(P, p0, p1, degree, self.M, self.world, means3D,
                                                base + 4 * self.campos_off, base + 4 * self.factors_off,
                                                dL_dsh, self.device)
+            if self.profile:
+                e_rb1.record()
+                self._pipe_marks.append((e_ready, e_bar, e_sum, e_rb0, e_rb1))
 
     def _make_streams(self):
         if self._side is None:
@@ -225,7 +240,16 @@ class NvlsExchange:
             cur.wait_stream(self._side2)
             self._piped = False
             self._pending = None
+            e_join = None
+            if self.profile:
+                e_join = torch.cuda.Event(enable_timing=True)
+                e_join.record()
             self.hdl.barrier(channel=0)    # sums broadcast everywhere; factor slots free for reuse
+            if self.profile and self._pipe_marks:
+                e_end = torch.cuda.Event(enable_timing=True)
+                e_end.record()
+                self._pipe_calls.append((self._pipe_marks, e_join, e_end))
+                self._pipe_marks = []
             return
         mark = self._mark
         mark("start")
@@ -274,6 +298,24 @@ class NvlsExchange:
     def profile_report(self):
         """Mean milliseconds per piece over the profiled calls (synchronises)."""
         torch.cuda.synchronize(self.device)
+        if self._pipe_calls:
+            # pipelined mode. Per Gaussian range j: wait_j = from "its backward preprocess is done on
+            # the main stream" to "every rank passed the barrier" (includes waiting for the slowest
+            # rank's range), sum_j = the in-switch sum, rebuild_j = the local dL_dsh rebuild (beside
+            # the sum). tail = from the LAST range's preprocess being done to the end of the
+            # exchange: the part of the exchange that nothing overlaps.
+            acc, calls = {}, len(self._pipe_calls)
+            for marks, e_join, e_end in self._pipe_calls:
+                for j, (e_ready, e_bar, e_sum, e_rb0, e_rb1) in enumerate(marks):
+                    for k, v in ((f"range{j}_barrier_wait", e_ready.elapsed_time(e_bar)),
+                                 (f"range{j}_in_switch_sum", e_bar.elapsed_time(e_sum)),
+                                 (f"range{j}_sh_rebuild", e_rb0.elapsed_time(e_rb1))):
+                        acc[k] = acc.get(k, 0.0) + v
+                last_ready = marks[-1][0]
+                acc["tail_after_last_preprocess"] = acc.get("tail_after_last_preprocess", 0.0) + last_ready.elapsed_time(e_end)
+                acc["barrier_out"] = acc.get("barrier_out", 0.0) + e_join.elapsed_time(e_end)
+            self._pipe_calls = []
+            return {k: round(v / calls, 4) for k, v in acc.items()}
         acc, n = {}, 0
         prev = None
         for name, e in self._marks:

@@ -64,6 +64,8 @@ def test_invalid_arguments_are_rejected_without_a_gpu(lib):
     assert lib.bgr_forward(None, cb, None, cb, None, cb, None, None, C.byref(n)) == -1
     assert b"null" in lib.bgr_last_error()
     assert lib.bgr_backward(None, None) == -1
+    assert lib.bgr_forward_raw(None, None, cb, None, cb, None, cb, None, None, C.byref(n)) == -1
+    assert lib.bgr_backward_raw(None, None, None, None) == -1
     assert lib.bgr_mark_visible(-1, None, None, None, None, None) == -1
 
 
