@@ -49,7 +49,7 @@ render_backward_kernel(int W, int H, const uint2* __restrict__ ranges,
     const uint32_t px = tile_px + lx, py = tile_py + ly;
     const bool inside = px < (uint32_t)W && py < (uint32_t)H;
     const size_t pix_id = (size_t)py * W + px;
-    const float pixfx = (float)px, pixfy = (float)py;
+    const float2 neg_pix = make_float2(-(float)px, -(float)py);
     const float rx0 = (float)tile_px, ry0 = (float)tile_py;
     const float rx1 = (float)min(tile_px + TILE_X - 1, (uint32_t)W - 1);
     const float ry1 = (float)min(tile_py + TILE_Y - 1, (uint32_t)H - 1);
@@ -122,8 +122,8 @@ render_backward_kernel(int W, int H, const uint2* __restrict__ ranges,
         }
         if (keep) {
             const int pos = before + __popc(kmask & ((1u << lane) - 1u));
-            s_geo[pos] = q0;
-            s_opa[pos] = make_float4(q1.x, q2.y, q1.y, __uint_as_float(li));
+            s_geo[pos] = make_float4(q0.x, q0.y, q1.x, q0.w);   // x, y, cz, cy
+            s_opa[pos] = make_float4(q0.z, q2.y, q1.y, __uint_as_float(li));   // cx, thr, opacity, list position
             s_col[pos] = make_float4(q1.z, q1.w, q2.x, __uint_as_float(id));
         }
         __syncthreads();
@@ -138,7 +138,7 @@ render_backward_kernel(int W, int H, const uint2* __restrict__ ranges,
             const float4 ta = s_geo[jt];
             const float4 tb = s_opa[jt];
             hit = __float_as_uint(tb.w) < wmax &&
-                  !tile_rejects(ta.x, ta.y, ta.z, ta.w, tb.x, tb.y, wx0, wy0, wx1, wy1);
+                  !tile_rejects(ta.x, ta.y, tb.x, ta.w, ta.z, tb.y, wx0, wy0, wx1, wy1);
         }
         unsigned hits = __ballot_sync(0xffffffffu, hit);
         while (hits) {
@@ -149,9 +149,10 @@ render_backward_kernel(int W, int H, const uint2* __restrict__ ranges,
             const float4 o = lds128(ja + PLANE_BYTES);
             const uint32_t pos_in_list = __float_as_uint(o.w);
             bool valid = pos_in_list < last_contributor;  // false for pixels outside the image
-            const float dx = a.x - pixfx;
-            const float dy = a.y - pixfy;
-            const float power = gauss_power(a.z, a.w, o.x, dx, dy);
+            const float2 dxy = add2(make_float2(a.x, a.y), neg_pix);   // mean - pixel
+            const float dx = dxy.x, dy = dxy.y;
+            float cxdx, czdy;
+            const float power = gauss_power2(o.x, make_float2(a.z, a.w), dxy, cxdx, czdy);
             valid = valid && !(power > 0.0f || power < o.y);
             if (!__any_sync(0xffffffffu, valid)) continue;
             const float G = expf(power);
@@ -189,22 +190,35 @@ render_backward_kernel(int W, int H, const uint2* __restrict__ ranges,
                 dL_dalpha = __fmaf_rn(bg_term, rcp_oma, dL_dalpha * T);
                 u = G * dL_dalpha;
             }
-            const float ux = u * dx, uy = u * dy;
-            float v0 = u * __fmaf_rn(a.w, dy, a.z * dx), v1 = u * __fmaf_rn(a.w, dx, o.x * dy);
-            float v2 = ux * dx, v3 = ux * dy, v4 = uy * dy, v5 = u;
-            float v6 = w * g0, v7 = w * g1, v8 = w * g2;
+            // moments, two per instruction where the operations pair up (FMUL2 / FFMA2)
+            const float2 uu = make_float2(u, u);
+            const float2 uxy = mul2(uu, dxy);                                   // u dx, u dy
+            const float2 s24 = mul2(uxy, dxy);                                  // u dx^2, u dy^2
+            const float2 lin = make_float2(__fmaf_rn(a.w, dy, cxdx), __fmaf_rn(a.w, dx, czdy));   // cx dx + cy dy, cz dy + cy dx
+            const float2 v01 = mul2(uu, lin);
+            const float2 v67 = mul2(make_float2(w, w), make_float2(g0, g1));
+            const float v3 = uxy.x * dy;
+            float v8 = w * g2;
 
             // Transposing butterfly: 8 values x 32 lanes -> each value summed over the warp.
+            // pairs: (v0, v1) | (v2 = Sxx, v3 = Sxy) | (v4 = Syy, v5 = u) | (v6, v7)
             const bool h1 = (lane & 16) != 0;
-            float w0 = (h1 ? v4 : v0) + __shfl_xor_sync(0xffffffffu, h1 ? v0 : v4, 16);
-            float w1 = (h1 ? v5 : v1) + __shfl_xor_sync(0xffffffffu, h1 ? v1 : v5, 16);
-            float w2 = (h1 ? v6 : v2) + __shfl_xor_sync(0xffffffffu, h1 ? v2 : v6, 16);
-            float w3 = (h1 ? v7 : v3) + __shfl_xor_sync(0xffffffffu, h1 ? v3 : v7, 16);
+            // (selects written per component: a float2 ?: becomes predicated moves)
+            const float2 k01 = make_float2(h1 ? s24.y : v01.x, h1 ? u : v01.y);         // kept: v4,v5 | v0,v1
+            const float2 k23 = make_float2(h1 ? v67.x : s24.x, h1 ? v67.y : v3);        //       v6,v7 | v2,v3
+            const float2 t01 = make_float2(h1 ? v01.x : s24.y, h1 ? v01.y : u);         // sent
+            const float2 t23 = make_float2(h1 ? s24.x : v67.x, h1 ? v3 : v67.y);
+            const float2 w01 = add2(k01, make_float2(__shfl_xor_sync(0xffffffffu, t01.x, 16),
+                                                     __shfl_xor_sync(0xffffffffu, t01.y, 16)));
+            const float2 w23 = add2(k23, make_float2(__shfl_xor_sync(0xffffffffu, t23.x, 16),
+                                                     __shfl_xor_sync(0xffffffffu, t23.y, 16)));
             const bool h2 = (lane & 8) != 0;
-            float u0 = (h2 ? w2 : w0) + __shfl_xor_sync(0xffffffffu, h2 ? w0 : w2, 8);
-            float u1 = (h2 ? w3 : w1) + __shfl_xor_sync(0xffffffffu, h2 ? w1 : w3, 8);
+            const float2 k2 = make_float2(h2 ? w23.x : w01.x, h2 ? w23.y : w01.y);
+            const float2 t2 = make_float2(h2 ? w01.x : w23.x, h2 ? w01.y : w23.y);
+            const float2 u01 = add2(k2, make_float2(__shfl_xor_sync(0xffffffffu, t2.x, 8),
+                                                    __shfl_xor_sync(0xffffffffu, t2.y, 8)));
             const bool h3 = (lane & 4) != 0;
-            float sacc = (h3 ? u1 : u0) + __shfl_xor_sync(0xffffffffu, h3 ? u0 : u1, 4);
+            float sacc = (h3 ? u01.y : u01.x) + __shfl_xor_sync(0xffffffffu, h3 ? u01.x : u01.y, 4);
             // ninth value: plain butterfly over lane bits 4..2, then it shares the last two
             // steps with the other eight (lanes with bit 1 set carry it from here on)
             v8 += __shfl_xor_sync(0xffffffffu, v8, 16);

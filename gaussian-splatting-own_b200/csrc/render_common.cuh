@@ -32,6 +32,34 @@ __device__ __forceinline__ float4 lds128(uint32_t addr)
 }
 constexpr uint32_t PLANE_BYTES = RENDER_THREADS * 16;
 
+// Packed FP32 pairs (sm_100: FMUL2 / FADD2 / FFMA2, one issue slot for two IEEE-rn operations).
+// Both render kernels are issue-bound, not pipe-bound, so pairing independent operations of the
+// same kind buys issue slots. Each half is rounded exactly like the scalar instruction.
+__device__ __forceinline__ float2 mul2(float2 a, float2 b)
+{
+    float2 r;
+    asm("{ .reg .b64 ra, rb, rr; mov.b64 ra, {%2,%3}; mov.b64 rb, {%4,%5}; mul.rn.f32x2 rr, ra, rb; "
+        "mov.b64 {%0,%1}, rr; }"
+        : "=f"(r.x), "=f"(r.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+    return r;
+}
+__device__ __forceinline__ float2 add2(float2 a, float2 b)
+{
+    float2 r;
+    asm("{ .reg .b64 ra, rb, rr; mov.b64 ra, {%2,%3}; mov.b64 rb, {%4,%5}; add.rn.f32x2 rr, ra, rb; "
+        "mov.b64 {%0,%1}, rr; }"
+        : "=f"(r.x), "=f"(r.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+    return r;
+}
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c)
+{
+    float2 r;
+    asm("{ .reg .b64 ra, rb, rc, rr; mov.b64 ra, {%2,%3}; mov.b64 rb, {%4,%5}; mov.b64 rc, {%6,%7}; "
+        "fma.rn.f32x2 rr, ra, rb, rc; mov.b64 {%0,%1}, rr; }"
+        : "=f"(r.x), "=f"(r.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y), "f"(c.x), "f"(c.y));
+    return r;
+}
+
 // Exactly the reference's evaluation order for the Gaussian exponent (forward.cu:335, SASS shape in
 // SURVEY.md A.5): power = -0.5*(cx*dx*dx + cz*dy*dy) - cy*dx*dy with
 //   t = (cz*dy)*dy, u = cx*dx, q = fma(u,dx,t), v = (cy*dx)*dy, power = fma(-0.5,q,-v).
@@ -42,6 +70,20 @@ __device__ __forceinline__ float gauss_power(float cx, float cy, float cz, float
     const float q = __fmaf_rn(u, dx, t);
     const float v = __fmul_rn(__fmul_rn(cy, dx), dy);
     return __fmaf_rn(-0.5f, q, -v);
+}
+
+// The same operations, the independent ones issued in pairs. The staged record keeps (cz, cy)
+// next to each other (s_geo = x, y, cz, cy; s_opa = cx, ...) so that the pair needs no moves:
+//   (czdy, cydx) = (cz, cy) * (dy, dx);  cxdx = cx*dx;  (t, v) = (czdy, cydx) * dy
+// czdy and cxdx are handed back: the backward's first moments reuse them.
+__device__ __forceinline__ float gauss_power2(float cx, float2 czcy, float2 d, float& cxdx, float& czdy)
+{
+    const float2 m = mul2(czcy, make_float2(d.y, d.x));
+    cxdx = __fmul_rn(cx, d.x);
+    czdy = m.x;
+    const float2 tv = mul2(m, make_float2(d.y, d.y));
+    const float q = __fmaf_rn(cxdx, d.x, tv.x);
+    return __fmaf_rn(-0.5f, q, -tv.y);
 }
 
 // Conservative tile-level rejection. Returns true when NO pixel centre of the rectangle

@@ -55,7 +55,7 @@ render_forward_kernel(int W, int H, const uint2* __restrict__ ranges,
     tile_pixel(tid, lx, ly);
     const uint32_t px = tile_px + lx, py = tile_py + ly;
     const bool inside = px < (uint32_t)W && py < (uint32_t)H;
-    const float pixfx = (float)px, pixfy = (float)py;
+    const float2 neg_pix = make_float2(-(float)px, -(float)py);
     // pixel-centre rectangle of the part of the tile that is inside the image
     const float rx0 = (float)tile_px, ry0 = (float)tile_py;
     const float rx1 = (float)min(tile_px + TILE_X - 1, (uint32_t)W - 1);
@@ -73,7 +73,8 @@ render_forward_kernel(int W, int H, const uint2* __restrict__ ranges,
     bool done = !inside;
     float T = 1.0f;
     uint32_t last_contributor = 0;
-    float C0 = 0.f, C1 = 0.f, C2 = 0.f;
+    float2 C01 = make_float2(0.f, 0.f);
+    float C2 = 0.f;
 
     for (int r = 0; r < rounds; ++r) {
         // all pixels finished -> stop fetching (also orders the previous round's smem reads
@@ -103,8 +104,8 @@ render_forward_kernel(int W, int H, const uint2* __restrict__ ranges,
         }
         if (keep) {
             const int pos = before + __popc(kmask & ((1u << lane) - 1u));
-            s_geo[pos] = q0;
-            s_opa[pos] = make_float4(q1.x, q2.y, q1.y, __uint_as_float((uint32_t)progress + 1u));
+            s_geo[pos] = make_float4(q0.x, q0.y, q1.x, q0.w);   // x, y, cz, cy
+            s_opa[pos] = make_float4(q0.z, q2.y, q1.y, __uint_as_float((uint32_t)progress + 1u));   // cx, thr, opacity
             s_col[pos] = make_float4(q1.z, q1.w, q2.x, 0.f);
         }
         __syncthreads();
@@ -119,7 +120,7 @@ render_forward_kernel(int W, int H, const uint2* __restrict__ ranges,
             if (jt < kept) {
                 const float4 a = s_geo[jt];
                 const float4 b = s_opa[jt];
-                hit = !tile_rejects(a.x, a.y, a.z, a.w, b.x, b.y, wx0, wy0, wx1, wy1);
+                hit = !tile_rejects(a.x, a.y, b.x, a.w, a.z, b.y, wx0, wy0, wx1, wy1);
             }
             unsigned hits = __ballot_sync(0xffffffffu, hit);
             while (hits) {
@@ -131,9 +132,9 @@ render_forward_kernel(int W, int H, const uint2* __restrict__ ranges,
                 const uint32_t ja = s_base + 16u * (uint32_t)j;
                 const float4 a = lds128(ja);
                 const float4 b = lds128(ja + PLANE_BYTES);
-                const float dx = a.x - pixfx;
-                const float dy = a.y - pixfy;
-                const float power = gauss_power(a.z, a.w, b.x, dx, dy);
+                float cxdx, czdy;
+                const float power = gauss_power2(b.x, make_float2(a.z, a.w),
+                                                 add2(make_float2(a.x, a.y), neg_pix), cxdx, czdy);
                 bool ok = !done && !(power > 0.0f || power < b.y);
                 if (kStats) st_exam += done ? 0 : 1;
                 const float alpha = fminf(0.99f, b.z * expf(power));
@@ -145,8 +146,7 @@ render_forward_kernel(int W, int H, const uint2* __restrict__ ranges,
                 ok = ok && !stop;
                 const float4 c = lds128(ja + 2 * PLANE_BYTES);
                 if (ok) {
-                    C0 = __fmaf_rn(__fmul_rn(c.x, alpha), T, C0);
-                    C1 = __fmaf_rn(__fmul_rn(c.y, alpha), T, C1);
+                    C01 = fma2(mul2(make_float2(c.x, c.y), make_float2(alpha, alpha)), make_float2(T, T), C01);
                     C2 = __fmaf_rn(__fmul_rn(c.z, alpha), T, C2);
                     T = test_T;
                     last_contributor = __float_as_uint(b.w);
@@ -169,8 +169,8 @@ render_forward_kernel(int W, int H, const uint2* __restrict__ ranges,
         final_T[pix_id] = T;
         n_contrib[pix_id] = last_contributor;
         const size_t plane = (size_t)H * W;
-        out_color[pix_id] = __fmaf_rn(T, bg[0], C0);
-        out_color[plane + pix_id] = __fmaf_rn(T, bg[1], C1);
+        out_color[pix_id] = __fmaf_rn(T, bg[0], C01.x);
+        out_color[plane + pix_id] = __fmaf_rn(T, bg[1], C01.y);
         out_color[2 * plane + pix_id] = __fmaf_rn(T, bg[2], C2);
     }
 }
