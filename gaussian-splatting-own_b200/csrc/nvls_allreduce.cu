@@ -11,7 +11,6 @@
 // the loads, all stores landed before consumers read) is provided by the caller with the symmetric
 // memory barrier before and after this kernel; the kernel itself never waits on another GPU.
 #include <algorithm>
-#include <cstdlib>
 #include "bgr_common.cuh"
 
 namespace bgr {
@@ -47,13 +46,6 @@ __device__ __forceinline__ void mm_st1(float* p, float v)
 constexpr int NVLS_THREADS = 512;
 constexpr int NVLS_UNROLL = 4;
 
-// TEMPORARY experiment switches (in-flight requests per CTA)
-static int env_int(const char* name, int dflt)
-{
-    const char* e = getenv(name);
-    return e ? atoi(e) : dflt;
-}
-
 __global__ void __launch_bounds__(NVLS_THREADS)
 nvls_allreduce_kernel(float* __restrict__ mc, size_t vec_begin, size_t vec_end, size_t tail_begin,
                       size_t tail_end)
@@ -84,22 +76,21 @@ struct NvlsSegments {
     size_t end[4];
 };
 
-template <int kThreads, int kUnroll>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(NVLS_THREADS)
 nvls_allreduce_segments_kernel(float* __restrict__ mc, NvlsSegments seg)
 {
     float4* mc4 = reinterpret_cast<float4*>(mc);
-    const size_t stride = (size_t)gridDim.x * kThreads;
+    const size_t stride = (size_t)gridDim.x * NVLS_THREADS;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         const size_t vec_end = seg.end[k];
-        size_t i = seg.begin[k] + (size_t)blockIdx.x * kThreads + threadIdx.x;
-        for (; i + (kUnroll - 1) * stride < vec_end; i += kUnroll * stride) {
-            float4 v[kUnroll];
+        size_t i = seg.begin[k] + (size_t)blockIdx.x * NVLS_THREADS + threadIdx.x;
+        for (; i + (NVLS_UNROLL - 1) * stride < vec_end; i += NVLS_UNROLL * stride) {
+            float4 v[NVLS_UNROLL];
 #pragma unroll
-            for (int u = 0; u < kUnroll; ++u) v[u] = mm_ld_reduce(mc4 + i + u * stride);
+            for (int u = 0; u < NVLS_UNROLL; ++u) v[u] = mm_ld_reduce(mc4 + i + u * stride);
 #pragma unroll
-            for (int u = 0; u < kUnroll; ++u) mm_st(mc4 + i + u * stride, v[u]);
+            for (int u = 0; u < NVLS_UNROLL; ++u) mm_st(mc4 + i + u * stride, v[u]);
         }
         for (; i < vec_end; i += stride) mm_st(mc4 + i, mm_ld_reduce(mc4 + i));
     }
@@ -153,19 +144,11 @@ int launch_nvls_allreduce_segments(void* multicast_ptr, int nseg, const size_t* 
         work = std::max(work, ve - vb);
     }
     if (work == 0) return 0;
-    static const int threads = env_int("BGR_NVLS_THREADS", 512), unroll = env_int("BGR_NVLS_UNROLL", 4);
-    size_t blocks = (work + (size_t)threads * unroll - 1) / ((size_t)threads * unroll);
+    size_t blocks = (work + (size_t)NVLS_THREADS * NVLS_UNROLL - 1) / ((size_t)NVLS_THREADS * NVLS_UNROLL);
     blocks = std::max<size_t>(1, std::min<size_t>(blocks, (size_t)std::max(1, max_blocks)));
     ++g_kernel_launches;
-    float* mcp = static_cast<float*>(multicast_ptr);
-    if (threads == 1024 && unroll == 8)
-        nvls_allreduce_segments_kernel<1024, 8><<<(unsigned)blocks, 1024, 0, s>>>(mcp, seg);
-    else if (threads == 1024)
-        nvls_allreduce_segments_kernel<1024, 4><<<(unsigned)blocks, 1024, 0, s>>>(mcp, seg);
-    else if (unroll == 8)
-        nvls_allreduce_segments_kernel<512, 8><<<(unsigned)blocks, 512, 0, s>>>(mcp, seg);
-    else
-        nvls_allreduce_segments_kernel<512, 4><<<(unsigned)blocks, 512, 0, s>>>(mcp, seg);
+    nvls_allreduce_segments_kernel<<<(unsigned)blocks, NVLS_THREADS, 0, s>>>(
+        static_cast<float*>(multicast_ptr), seg);
     return 0;
 }
 

@@ -127,8 +127,6 @@ class NvlsExchange:
         # 32 CTAs keep the fabric as busy and leave 116 SMs alone. Alone (dense) it gets 296.
         self.max_blocks = self._max_blocks_arg if self._max_blocks_arg is not None else \
             (32 if mode == "factor" else 296)
-        import os
-        self.last_blocks = int(os.environ.get("BGR_NVLS_LAST_BLOCKS", self.max_blocks))   # TEMPORARY experiment switch
         total = self.factors_off + (world * P * 3 if mode == "factor" else 0)
         self.buf = symm_mem.empty(total, dtype=torch.float32, device=self.device)
         self.hdl = symm_mem.rendezvous(self.buf, grp)
@@ -208,10 +206,8 @@ class NvlsExchange:
             # rebuild and the next range's preprocess fill the rest of the machine around it
             segs = [(leaf0 + 3 * p0, 3 * n), (leaf0 + 3 * P + p0, n), (leaf0 + 4 * P + 3 * p0, 3 * n),
                     (leaf0 + 7 * P + 4 * p0, 4 * n)]   # means3D | opacity | scales | rotations rows
-            # the last range's sum has only that range's rebuild beside it: it may take more SMs
-            blocks = self.last_blocks if p1 >= P else self.max_blocks
             self._C.nvls_allreduce_segments(self.hdl.multicast_ptr, segs, self.rank, self.world,
-                                            self.device, blocks)
+                                            self.device, self.max_blocks)
             if self.profile:
                 e_sum.record()
         self._side2.wait_event(ready)
