@@ -84,13 +84,16 @@ def main():
             allowed = max(3.0 * spread[name], 2e-5)
             good = frac <= allowed and worst <= 1e-3 * mag and bool(torch.isfinite(got).all())
             ok = ok and good
-            print(f"[rank {rank}/{world} {time.time() - t0:5.1f}s] mode={ex.mode} chunks={ex.chunks} it={it} {name}: "
-                  f"outside 1e-4/1e-6 bar {frac:.2e} (same-rank run-to-run {spread[name]:.2e}, allowed {allowed:.2e}) "
-                  f"max err {worst:.3e} of |g|max {mag:.3e} identical_to_peer {ident} {'ok' if good else 'FAIL'}",
-                  flush=True)
+            sys.stdout.write(
+                f"[rank {rank}/{world} {time.time() - t0:5.1f}s] mode={ex.mode} chunks={ex.chunks} it={it} {name}: "
+                f"outside 1e-4/1e-6 bar {frac:.2e} (same-rank run-to-run {spread[name]:.2e}, allowed {allowed:.2e}) "
+                f"max err {worst:.3e} of |g|max {mag:.3e} identical_to_peer {ident} {'ok' if good else 'FAIL'}\n")
+            sys.stdout.flush()
         ex.hdl.barrier(channel=0)   # nobody overwrites its arena while a peer still compares
         torch.cuda.synchronize()
-    print(f"DP_CHECK rank {rank} world {world}", "PASS" if ok else "FAIL", flush=True)
+    # one write per line: eight ranks share the launcher's pipe
+    sys.stdout.write(f"DP_CHECK rank {rank} world {world} {'PASS' if ok else 'FAIL'}\n")
+    sys.stdout.flush()
     os._exit(0 if ok else 1)
 
 
