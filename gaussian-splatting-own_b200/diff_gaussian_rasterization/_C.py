@@ -13,6 +13,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import threading
 from pathlib import Path
 
 import torch
@@ -157,7 +158,28 @@ def _f32c(t: torch.Tensor, dev) -> torch.Tensor:
 
 
 def _stream(dev) -> int:
-    return torch.cuda.current_stream(dev).cuda_stream
+    # raw handle of the current stream (what torch.cuda.current_stream(dev).cuda_stream returns,
+    # without building the Stream object: this runs two or three times per training step)
+    return torch._C._cuda_getCurrentRawStream(dev.index if dev.index is not None else torch.cuda.current_device())
+
+
+class _on_device:
+    """`with torch.cuda.device(dev)` that costs nothing when dev is already current."""
+
+    __slots__ = ("ctx",)
+
+    def __init__(self, dev):
+        idx = dev.index
+        self.ctx = None if idx is None or idx == torch.cuda.current_device() else torch.cuda.device(dev)
+
+    def __enter__(self):
+        if self.ctx is not None:
+            self.ctx.__enter__()
+
+    def __exit__(self, *exc):
+        if self.ctx is not None:
+            return self.ctx.__exit__(*exc)
+        return False
 
 
 class _Grower:
@@ -171,7 +193,7 @@ class _Grower:
     __slots__ = ("box", "cb")
 
     def __init__(self, dev):
-        box = [torch.empty(0, dtype=torch.uint8, device=dev)]
+        box = [None]
 
         def grow(nbytes, _user):
             try:
@@ -183,9 +205,25 @@ class _Grower:
         self.box = box
         self.cb = _ALLOC_FN(grow)
 
-    @property
-    def tensor(self):
-        return self.box[0]
+    def take(self, dev):
+        """The tensor the core asked for (an empty one if it never did); the grower forgets it."""
+        t, self.box[0] = self.box[0], None
+        return t if t is not None else torch.empty(0, dtype=torch.uint8, device=dev)
+
+
+_grower_pool = threading.local()
+
+
+def _take_growers(dev):
+    """Three growers (geometry, binning, image) for one forward call. Building a ctypes callback
+    costs several microseconds, so finished calls park theirs per thread and device."""
+    pool = _grower_pool.__dict__.setdefault("free", {})
+    g = pool.pop(dev, None)
+    return g if g is not None else (_Grower(dev), _Grower(dev), _Grower(dev))
+
+
+def _park_growers(dev, g):
+    _grower_pool.__dict__.setdefault("free", {})[dev] = g
 
 
 def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier,
@@ -199,13 +237,14 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
     L = lib()
     dev = means3D.device
     P, H, W = int(means3D.size(0)), int(image_height), int(image_width)
-    geom, binning, img = _Grower(dev), _Grower(dev), _Grower(dev)
-    with torch.cuda.device(dev):
+    growers = _take_growers(dev)
+    geom, binning, img = growers
+    with _on_device(dev):
         out_color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
         radii = torch.empty((P,), dtype=torch.int32, device=dev)
         if P == 0:
             out_color.zero_()
-            return 0, out_color, radii, geom.tensor, binning.tensor, img.tensor
+            return 0, out_color, radii, geom.take(dev), binning.take(dev), img.take(dev)
         M = int(sh.size(1)) if sh.size(0) != 0 else 0
         keep = [_f32c(t, dev) for t in (background, means3D, sh, colors, opacity, scales, rotations,
                                         cov3D_precomp, viewmatrix, projmatrix, campos)]
@@ -221,7 +260,9 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         rc = L.bgr_forward(C.byref(a), geom.cb, None, binning.cb, None, img.cb, None,
                            _stream(dev), C.byref(rendered))
         _check(rc)
-    return int(rendered.value), out_color, radii, geom.tensor, binning.tensor, img.tensor
+    bufs = (geom.take(dev), binning.take(dev), img.take(dev))
+    _park_growers(dev, growers)
+    return (int(rendered.value), out_color, radii) + bufs
 
 
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations,
@@ -235,7 +276,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     P = int(means3D.size(0))
     H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
     M = int(sh.size(1)) if sh.size(0) != 0 else 0
-    with torch.cuda.device(dev):
+    with _on_device(dev):
         # One arena for all outputs: every element is written by the kernels, so no zero fill is
         # needed. Layout (floats per Gaussian):
         #   [means2D 3 | colors 3 | cov3D 6 || means3D 3 | opacity 1 | scales 3 | rotations 4 | sh 3M]
@@ -301,8 +342,8 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
                     a.gaussian_begin, a.gaussian_end = int(p0), int(p1)
                     _check(L.bgr_backward(C.byref(a), _stream(dev)))
                     after_chunk(int(p0), int(p1))
-            # scratch may be reused by the allocator only after the kernels that read it
-            scratch.record_stream(torch.cuda.current_stream(dev))
+            # scratch was allocated on the stream the kernels run on: the caching allocator hands
+            # it out again only to later work of that same stream, so no record_stream is needed
     return (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales,
             dL_drotations)
 
@@ -322,13 +363,14 @@ def rasterize_gaussians_raw(background, xyz, opacity_raw, scaling_raw, rotation_
     L = lib()
     dev = xyz.device
     P, H, W = int(xyz.size(0)), int(image_height), int(image_width)
-    geom, binning, img = _Grower(dev), _Grower(dev), _Grower(dev)
-    with torch.cuda.device(dev):
+    growers = _take_growers(dev)
+    geom, binning, img = growers
+    with _on_device(dev):
         out_color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
         radii = torch.empty((P,), dtype=torch.int32, device=dev)
         if P == 0:
             out_color.zero_()
-            return 0, out_color, radii, geom.tensor, binning.tensor, img.tensor
+            return 0, out_color, radii, geom.take(dev), binning.take(dev), img.take(dev)
         if features_dc.dim() != 3 or features_dc.size(1) != 1 or features_rest.dim() != 3:
             raise RuntimeError("features_dc must be (P,1,3) and features_rest (P,M-1,3)")
         M = 1 + int(features_rest.size(1))
@@ -346,7 +388,9 @@ def rasterize_gaussians_raw(background, xyz, opacity_raw, scaling_raw, rotation_
         rc = L.bgr_forward_raw(C.byref(a), _ptr(rest_), geom.cb, None, binning.cb, None, img.cb, None,
                                _stream(dev), C.byref(rendered))
         _check(rc)
-    return int(rendered.value), out_color, radii, geom.tensor, binning.tensor, img.tensor
+    bufs = (geom.take(dev), binning.take(dev), img.take(dev))
+    _park_growers(dev, growers)
+    return (int(rendered.value), out_color, radii) + bufs
 
 
 def rasterize_gaussians_raw_backward(background, xyz, radii, scaling_raw, rotation_raw, scale_modifier,
@@ -361,7 +405,7 @@ def rasterize_gaussians_raw_backward(background, xyz, radii, scaling_raw, rotati
     P = int(xyz.size(0))
     H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
     M = 1 + int(features_rest.size(1))
-    with torch.cuda.device(dev):
+    with _on_device(dev):
         # one arena; [colors 3 | cov3D 6] are by-products nobody reads on this path
         widths = (3, 3, 6, 3, 1, 3, 4, 3, 3 * (M - 1))
         arena = torch.empty((P * sum(widths),), dtype=torch.float32, device=dev)
@@ -391,7 +435,6 @@ def rasterize_gaussians_raw_backward(background, xyz, radii, scaling_raw, rotati
                 dL_dmean3D=_ptr(dL_dxyz), dL_dcov3D=_ptr(dL_dcov3D), dL_dsh=_ptr(dL_ddc),
                 dL_dscale=_ptr(dL_dscaling), dL_drot=_ptr(dL_drotation), debug=int(bool(debug)))
             _check(L.bgr_backward_raw(C.byref(a), _ptr(rest_), _ptr(dL_drest), _stream(dev)))
-            scratch.record_stream(torch.cuda.current_stream(dev))
     return dL_dmeans2D, dL_dopacity, dL_dxyz, dL_ddc, dL_drest, dL_dscaling, dL_drotation
 
 
@@ -401,7 +444,7 @@ def mark_visible(means3D, viewmatrix, projmatrix):
         raise RuntimeError("the rasterizer is CUDA-only: means3D must be a CUDA tensor")
     dev = means3D.device
     P = int(means3D.size(0))
-    with torch.cuda.device(dev):
+    with _on_device(dev):
         present = torch.zeros((P,), dtype=torch.bool, device=dev)
         if P != 0:
             m, v, pj = _f32c(means3D, dev), _f32c(viewmatrix, dev), _f32c(projmatrix, dev)
@@ -520,7 +563,7 @@ def render_stats(fwd_out, P, W, H) -> dict:
     R, _c, _r, geom, binning, img = fwd_out
     out = (C.c_ulonglong * 4)()
     dev = geom.device
-    with torch.cuda.device(dev):
+    with _on_device(dev):
         _check(lib().bgr_render_stats(int(P), int(R), int(W), int(H), _ptr(geom), _ptr(binning),
                                       _ptr(img), out, _stream(dev)))
     return dict(zip(("staged", "examined", "exp_evaluated", "blended"), [int(x) for x in out]))
@@ -551,7 +594,7 @@ def radix_sort(keys: torch.Tensor, values: torch.Tensor | None, bit_lo: int, bit
     L = lib()
     dev = keys.device
     n = keys.numel()
-    with torch.cuda.device(dev):
+    with _on_device(dev):
         ka = keys.contiguous().clone()
         kb = torch.empty_like(ka)
         va = values.contiguous().clone() if values is not None else None
@@ -571,7 +614,7 @@ def inclusive_scan_u32(x: torch.Tensor) -> torch.Tensor:
     L = lib()
     dev = x.device
     n = x.numel()
-    with torch.cuda.device(dev):
+    with _on_device(dev):
         xin = x.contiguous()
         out = torch.empty_like(xin)
         temp = torch.empty((L.bgr_scan_temp_bytes(n),), dtype=torch.uint8, device=dev)
