@@ -160,6 +160,8 @@ def _f32c(t: torch.Tensor, dev) -> torch.Tensor:
 def _stream(dev) -> int:
     # raw handle of the current stream (what torch.cuda.current_stream(dev).cuda_stream returns,
     # without building the Stream object: this runs two or three times per training step)
+    if not isinstance(dev, torch.device):
+        dev = torch.device(dev) if not isinstance(dev, int) else torch.device("cuda", dev)
     return torch._C._cuda_getCurrentRawStream(dev.index if dev.index is not None else torch.cuda.current_device())
 
 
