@@ -10,7 +10,7 @@
 #include "bgr_common.cuh"
 
 namespace bgr {
-unsigned long long g_kernel_launches = 0;
+std::atomic<unsigned long long> g_kernel_launches{0};
 }
 
 namespace {
@@ -99,7 +99,7 @@ extern "C" {
 BGR_API const char* bgr_last_error(void) { return g_last_error.c_str(); }
 BGR_API const char* bgr_version(void) { return "bgr 0.1 (sm_100a)"; }
 
-BGR_API unsigned long long bgr_launch_count(void) { return bgr::g_kernel_launches; }
+BGR_API unsigned long long bgr_launch_count(void) { return bgr::g_kernel_launches.load(std::memory_order_relaxed); }
 BGR_API void bgr_last_forward_info(int* out8) { std::copy(g_forward_info, g_forward_info + 8, out8); }
 
 BGR_API void bgr_stage_timing(int enable)
@@ -459,12 +459,16 @@ BGR_API int bgr_render_stats(int P, int R, int width, int height, const void* ge
     unsigned long long* dev = nullptr;
     int rc;
     if ((rc = check_cuda(cudaMalloc(reinterpret_cast<void**>(&dev), 4 * sizeof(unsigned long long)), "cudaMalloc"))) return rc;
-    cudaMemsetAsync(dev, 0, 4 * sizeof(unsigned long long), s);
+    if ((rc = check_cuda(cudaMemsetAsync(dev, 0, 4 * sizeof(unsigned long long), s), "memset stats"))) {
+        cudaFree(dev);
+        return rc;
+    }
     launch_render_stats(width, height, reinterpret_cast<const uint2*>(img + IL.ranges),
                         reinterpret_cast<const uint32_t*>(bin + BL.point_list),
                         reinterpret_cast<const GaussRec*>(geom + GL.rec), dev, s);
-    cudaMemcpyAsync(stats4_host, dev, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s);
-    rc = check_cuda(cudaStreamSynchronize(s), "render stats");
+    rc = check_cuda(cudaMemcpyAsync(stats4_host, dev, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s),
+                    "copy stats");
+    if (rc == 0) rc = check_cuda(cudaStreamSynchronize(s), "render stats");
     cudaFree(dev);
     return rc;
 }

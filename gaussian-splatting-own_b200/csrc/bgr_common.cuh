@@ -1,5 +1,6 @@
 // Shared declarations for the sm_100a rasterizer kernels (internal; the public ABI is include/bgr.h).
 #pragma once
+#include <atomic>
 #include <cstdint>
 #include <cstddef>
 #include <cuda_runtime.h>
@@ -46,7 +47,7 @@ struct BinningLayout {
 };
 
 // Number of kernels this library has launched (diagnostic; bumped by every launch_* wrapper).
-extern unsigned long long g_kernel_launches;
+extern std::atomic<unsigned long long> g_kernel_launches;   // several host threads may launch
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 

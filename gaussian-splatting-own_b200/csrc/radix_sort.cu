@@ -237,22 +237,20 @@ int radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* v
     uint32_t* hist = reinterpret_cast<uint32_t*>(tb + L.hist);
     uint32_t* tickets = reinterpret_cast<uint32_t*>(tb + L.tickets);
     uint32_t* status = reinterpret_cast<uint32_t*>(tb + L.status);
-    cudaMemsetAsync(tb, 0, L.status + (size_t)npasses * L.nblocks * RADIX * 4, s);
+    if (cudaMemsetAsync(tb, 0, L.status + (size_t)npasses * L.nblocks * RADIX * 4, s) != cudaSuccess) return -1;
 
     // function attributes are per device (context): opt in once on each device that sorts
     static std::atomic<unsigned long long> attr_done_mask{0};
     int dev = 0;
-    cudaGetDevice(&dev);
+    if (cudaGetDevice(&dev) != cudaSuccess) return -1;
     const unsigned long long dev_bit = 1ull << (dev & 63);
     if ((attr_done_mask.load(std::memory_order_relaxed) & dev_bit) == 0) {
-        cudaFuncSetAttribute(onesweep_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)onesweep_smem(false));
-        cudaFuncSetAttribute(onesweep_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)onesweep_smem(false));
-        cudaFuncSetAttribute(onesweep_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)onesweep_smem(true));
-        cudaFuncSetAttribute(onesweep_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)onesweep_smem(true));
+        const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
+        if (cudaFuncSetAttribute(onesweep_kernel<false, false>, attr, (int)onesweep_smem(false)) != cudaSuccess ||
+            cudaFuncSetAttribute(onesweep_kernel<false, true>, attr, (int)onesweep_smem(false)) != cudaSuccess ||
+            cudaFuncSetAttribute(onesweep_kernel<true, false>, attr, (int)onesweep_smem(true)) != cudaSuccess ||
+            cudaFuncSetAttribute(onesweep_kernel<true, true>, attr, (int)onesweep_smem(true)) != cudaSuccess)
+            return -1;
         attr_done_mask.fetch_or(dev_bit, std::memory_order_relaxed);
     }
 
