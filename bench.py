@@ -250,7 +250,7 @@ def make_e2e_step(backend, wl, world, impl):
     leaves = {k: v.clone().requires_grad_(True) for k, v in wl.scene.items()}
     h2d = cam_host.numel() * 4 + w_host.numel() * 4
     # The loss weights are first needed after the forward: their copy runs on a second stream
-    # under the forward's compositing kernels (both arms use this harness). The step ends with a
+    # under the forward kernels (both arms use this harness). The step ends with a
     # synchronize, so the next step's copy cannot overtake this step's reads.
     copy_stream = torch.cuda.Stream(device=dev)
     w_ready = torch.cuda.Event()
@@ -259,6 +259,11 @@ def make_e2e_step(backend, wl, world, impl):
 
     def step():
         cam_dev.copy_(cam_host, non_blocking=True)
+        # queued first: with eight ranks sharing the host's memory system the 24.9 MB copy takes
+        # longer than alone, and it needs the whole forward to hide under
+        with torch.cuda.stream(copy_stream):
+            w_dev.copy_(w_host, non_blocking=True)
+            w_ready.record(copy_stream)
         for t in leaves.values():
             t.grad = None
         settings = dgr.GaussianRasterizationSettings(
@@ -271,12 +276,6 @@ def make_e2e_step(backend, wl, world, impl):
             means3D=leaves["means3D"], means2D=means2D, shs=leaves["shs"], colors_precomp=None,
             opacities=leaves["opacities"], scales=leaves["scales"], rotations=leaves["rotations"],
             cov3D_precomp=None)
-        # (queued after the rasterizer call, which returns once the preprocess has run: the copy
-        # still has the whole compositing pass to hide under, and the host reaches the first
-        # kernel launch of the step sooner)
-        with torch.cuda.stream(copy_stream):
-            w_dev.copy_(w_host, non_blocking=True)
-            w_ready.record(copy_stream)
         torch.cuda.current_stream().wait_event(w_ready)
         loss = (color * w_dev).sum()
         if nvls is not None:
