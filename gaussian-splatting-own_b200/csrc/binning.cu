@@ -533,6 +533,7 @@ tile_sort_kernel(const uint2* __restrict__ ranges, uint64_t* __restrict__ keys, 
         uint32_t place[TS_KEYS_PER_THREAD];
 #pragma unroll
         for (int k = 0; k < TS_KEYS_PER_THREAD; ++k) {
+            if ((uint32_t)k * kThreads >= n) break;      // block-uniform: the list ends here
             const uint32_t i = (uint32_t)tid + (uint32_t)k * kThreads;
             place[k] = 0;
             if (i < n) {
@@ -584,6 +585,7 @@ tile_sort_kernel(const uint2* __restrict__ ranges, uint64_t* __restrict__ keys, 
             // place = bin base + arrival number; the bucket lands in shared memory bin by bin
 #pragma unroll
             for (int k = 0; k < TS_KEYS_PER_THREAD; ++k) {
+                if ((uint32_t)k * kThreads >= n) break;
                 const uint32_t i = (uint32_t)tid + (uint32_t)k * kThreads;
                 if (i < n) {
                     const uint64_t key = bucket[i];
@@ -595,6 +597,7 @@ tile_sort_kernel(const uint2* __restrict__ ranges, uint64_t* __restrict__ keys, 
             // 4. order inside the bin: count the smaller keys of the own bin
 #pragma unroll
             for (int k = 0; k < TS_KEYS_PER_THREAD; ++k) {
+                if ((uint32_t)k * kThreads >= n) break;
                 const uint32_t i = (uint32_t)tid + (uint32_t)k * kThreads;
                 if (i < n) {
                     const uint64_t key = s_keys[place[k]];
@@ -687,8 +690,11 @@ int launch_tile_sort(uint32_t num_tiles, const uint2* ranges, uint64_t* keys, ui
     while (max_bin_bits < TS_MAX_BIN_BITS && (1u << max_bin_bits) < (2u << TS_BINS_PER_KEY_LOG2) * smem_keys) ++max_bin_bits;
     const size_t smem = tile_sort_smem_bytes(smem_keys, max_bin_bits);
     ++g_kernel_launches;
-    // 16 keys per thread at most: the block size follows the longest list
-    if (smem_keys <= 4 * 32 * TS_KEYS_PER_THREAD)
+    // Block size by the longest list (16 keys per thread at most). Measured on 1M-10M Gaussians at
+    // 4K and 3M / 6M at 1080p: four warps are best up to 1 024 keys, eight from there to 4 096
+    // (e.g. longest list 1 802: 0.68 / 0.56 / 0.76 ms with 4 / 8 / 16 warps); more warps only when
+    // the keys-per-thread limit demands them (4 950: 1.62 ms with 16 warps, 2.35 with 32).
+    if (smem_keys <= 1024)
         tile_sort_kernel<4><<<num_tiles, 128, smem, s>>>(ranges, keys, keys_alt, nb_idx, smem_keys, max_bin_bits, point_list);
     else if (smem_keys <= 8 * 32 * TS_KEYS_PER_THREAD)
         tile_sort_kernel<8><<<num_tiles, 256, smem, s>>>(ranges, keys, keys_alt, nb_idx, smem_keys, max_bin_bits, point_list);
