@@ -204,3 +204,21 @@ def test_boundary_extension_builds_and_exposes_the_reference_signatures():
                                          torch.Tensor([]), torch.Tensor([]), 1.0, torch.Tensor([]),
                                          torch.eye(4), torch.eye(4), 1.0, 1.0, 16, 16, torch.Tensor([]), 3,
                                          torch.zeros(3), False, False)
+
+
+def test_raw_leaf_entry_surface():
+    """The extended entry beside the drop-in one: names, arities, and the same
+    loud failure on CPU tensors."""
+    import diff_gaussian_rasterization as d
+    assert issubclass(d._RasterizeGaussiansRaw, torch.autograd.Function)
+    sig = inspect.signature(d.RawGaussianRasterizer.forward)
+    assert list(sig.parameters) == ["self", "xyz", "means2D", "features_dc", "features_rest", "opacity_raw",
+                                    "scaling_raw", "rotation_raw"]
+    assert len(inspect.signature(d._C.rasterize_gaussians_raw).parameters) == 18
+    assert len(inspect.signature(d._C.rasterize_gaussians_raw_backward).parameters) == 20
+    r = d.RawGaussianRasterizer(_settings(d))
+    z = torch.zeros
+    with pytest.raises(RuntimeError, match="CUDA-only"):
+        r(z(4, 3), z(4, 3), z(4, 1, 3), z(4, 15, 3), z(4, 1), z(4, 3), z(4, 4))
+    with pytest.raises(RuntimeError, match="num_points, 3"):
+        d._C.rasterize_gaussians_raw(z(3), z(4, 2), *([torch.Tensor([])] * 16))
