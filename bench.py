@@ -55,11 +55,13 @@ def parse_args():
     ap.add_argument("--impl", choices=("ours", "reference", "reference-ext"), default="ours")
     ap.add_argument("--gaussians", type=int, default=3_000_000)
     ap.add_argument("--res", choices=("800x800", "1080p", "4k"), default="1080p")
-    ap.add_argument("--mode", choices=("step", "sweep", "f1"), default="step",
+    ap.add_argument("--mode", choices=("step", "sweep", "f1", "train"), default="step",
                     help="step: the train-step bench (default). sweep: BASELINE.json configs[4], the "
                          "forward-only 4K grid over Gaussians x SH degree x scale_modifier, both arms "
                          "per cell, written to --out. f1: the trainer's activation glue + drop-in path "
-                         "against the raw-leaf entry with the activations fused (SURVEY.md 8 row f1)")
+                         "against the raw-leaf entry with the activations fused (SURVEY.md 8 row f1). "
+                         "train: one whole training iteration (activations, rasterizer, L1 + D-SSIM loss, Adam) "
+                         "composed as the reference's trainer does vs the fused entries (rows f1 + f2)")
     ap.add_argument("--sweep-gaussians", default="1,2,5,10", help="millions of Gaussians per cell")
     ap.add_argument("--sweep-degrees", default="0,3")
     ap.add_argument("--sweep-mods", default="0.5,1,2")
@@ -553,6 +555,96 @@ def run_f1(args, device):
 
 
 # --------------------------------------------------------------------------------------------
+# f1 + f2: a whole training iteration, composed as the reference's trainer does vs fused
+# --------------------------------------------------------------------------------------------
+def run_train(args, device):
+    """One training iteration of train.py:79-128 without densification, CUDA-event timed, inputs
+    resident: activations (scene/gaussian_model.py:95-115) -> rasterizer -> loss = 0.8 L1 + 0.2
+    (1 - SSIM) (utils/loss_utils.py) -> backward -> Adam over the six groups (gaussian_model.py:
+    149-160) -> zero_grad. Three ways: the reference's rasterizer with torch loss and
+    torch.optim.Adam ("reference"), this library's drop-in rasterizer in the same composition
+    ("drop_in"), and the fused entries RawGaussianRasterizer + l1_ssim_loss + FusedAdam ("fused")."""
+    import math
+    import torch.nn.functional as F
+    import diff_gaussian_rasterization as dgr
+    import train_step
+    load_backend("ours")
+    ref = load_backend("reference")
+    wl = Workload(args, 0, device)
+    s, c = wl.scene, wl.cam
+    o = s["opacities"].clamp(1e-4, 1 - 1e-4)
+    raw0 = {"xyz": s["means3D"], "f_dc": s["shs"][:, :1, :].contiguous(), "f_rest": s["shs"][:, 1:, :].contiguous(),
+            "opacity": torch.log(o / (1 - o)), "scaling": torch.log(s["scales"]), "rotation": s["rotations"] * 1.25}
+    lrs = {"xyz": 0.00016, "f_dc": 0.0025, "f_rest": 0.0025 / 20.0, "opacity": 0.05, "scaling": 0.005,
+           "rotation": 0.001}
+    gt = (torch.rand(3, wl.H, wl.W, generator=torch.Generator().manual_seed(3))).to(device)
+    settings = dgr.GaussianRasterizationSettings(
+        image_height=wl.H, image_width=wl.W, tanfovx=c.tanfovx, tanfovy=c.tanfovy, bg=wl.bg,
+        scale_modifier=1.0, viewmatrix=wl.view, projmatrix=wl.proj, sh_degree=3, campos=wl.campos,
+        prefiltered=False, debug=False)
+    g1 = torch.tensor([math.exp(-(x - 5) ** 2 / float(2 * 1.5 ** 2)) for x in range(11)])
+    g1 = (g1 / g1.sum()).unsqueeze(1)
+    window = g1.mm(g1.t()).float()[None, None].expand(3, 1, 11, 11).contiguous().to(device)
+
+    def torch_loss(img):          # utils/loss_utils.py:16-63, train.py:91-92
+        conv = lambda t: F.conv2d(t[None], window, padding=5, groups=3)[0]  # noqa: E731
+        mu1, mu2 = conv(img), conv(gt)
+        s1, s2, s12 = conv(img * img) - mu1 * mu1, conv(gt * gt) - mu2 * mu2, conv(img * gt) - mu1 * mu2
+        ssim = (((2 * mu1 * mu2 + 0.0001) * (2 * s12 + 0.0009)) /
+                ((mu1 * mu1 + mu2 * mu2 + 0.0001) * (s1 + s2 + 0.0009))).mean()
+        return 0.8 * (img - gt).abs().mean() + 0.2 * (1.0 - ssim)
+
+    def make(kind):
+        P_ = {k: torch.nn.Parameter(v.clone()) for k, v in raw0.items()}
+        groups = [{"params": [P_[k]], "lr": lrs[k], "name": k} for k in raw0]
+        if kind == "fused":
+            opt = train_step.FusedAdam(groups, lr=0.0, eps=1e-15)
+            rast = dgr.RawGaussianRasterizer(settings)
+
+            def step():
+                m2d = torch.zeros_like(P_["xyz"], requires_grad=True)
+                img, _ = rast(P_["xyz"], m2d, P_["f_dc"], P_["f_rest"], P_["opacity"], P_["scaling"], P_["rotation"])
+                train_step.l1_ssim_loss(img, gt, 0.2).backward()
+                opt.step()
+                opt.zero_grad(set_to_none=True)
+            return step
+        opt = torch.optim.Adam(groups, lr=0.0, eps=1e-15)
+        if kind == "reference":
+            fn = dgr.make_rasterize_function(ref)
+
+            class Rast(dgr.GaussianRasterizer):
+                _rasterize = staticmethod(lambda *a: fn.apply(*a))
+                _backend = ref
+        else:
+            Rast = dgr.GaussianRasterizer
+        rast = Rast(settings)
+
+        def step():
+            m2d = torch.zeros_like(P_["xyz"], requires_grad=True)
+            img, _ = rast(means3D=P_["xyz"], means2D=m2d, opacities=torch.sigmoid(P_["opacity"]),
+                          shs=torch.cat((P_["f_dc"], P_["f_rest"]), dim=1), scales=torch.exp(P_["scaling"]),
+                          rotations=F.normalize(P_["rotation"]))
+            torch_loss(img).backward()
+            opt.step()
+            opt.zero_grad(set_to_none=True)
+        return step
+
+    out = {"mode": "train", "metric": "ms per training iteration (activations + rasterizer + L1/D-SSIM loss + Adam)",
+           "config": {"workload": f"{args.gaussians} Gaussians SH3, {args.res}, one view per iteration, inputs resident"},
+           "steps": args.steps, "warmup": args.warmup}
+    kinds = (["reference"] if ref is not None else []) + ["drop_in", "fused"]
+    for kind in kinds:
+        step = make(kind)
+        out[f"{kind}_ms"] = round(timed(step, args.steps, args.warmup, 1, device) / args.steps, 4)
+        del step
+        torch.cuda.empty_cache()
+    if "reference_ms" in out:
+        out["speedup_vs_reference"] = round(out["reference_ms"] / out["fused_ms"], 3)
+    out["speedup_vs_drop_in"] = round(out["drop_in_ms"] / out["fused_ms"], 3)
+    print(json.dumps(out))
+
+
+# --------------------------------------------------------------------------------------------
 # configs[4]: render-only sweep at 3840x2160 (tile-list length and sort-size stress)
 # --------------------------------------------------------------------------------------------
 def run_sweep(args, device):
@@ -681,6 +773,11 @@ def main():
         if world > 1 or args.impl != "ours":
             raise SystemExit("--mode f1 is a single-GPU run of this library")
         run_f1(args, device)
+        return
+    if args.mode == "train":
+        if world > 1 or args.impl != "ours":
+            raise SystemExit("--mode train is a single-GPU run (it times all arms itself)")
+        run_train(args, device)
         return
 
     wl = Workload(args, rank, device)

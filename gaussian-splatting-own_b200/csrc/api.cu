@@ -426,6 +426,32 @@ BGR_API int bgr_backward_raw(const BgrBackwardArgs* a, const float* features_res
     return backward_impl(a, true, features_rest, dL_dfeatures_rest, stream_v);
 }
 
+BGR_API size_t bgr_loss_scratch_bytes(int width, int height)
+{
+    return (width > 0 && height > 0) ? bgr::loss_scratch_bytes(width, height) : 0;
+}
+
+BGR_API int bgr_l1_ssim_loss(const float* image, const float* gt, int width, int height, float lambda_dssim,
+                             void* scratch, float* loss3, float* dL_dimage, void* stream_v)
+{
+    cudaStream_t s = static_cast<cudaStream_t>(stream_v);
+    if (bgr::launch_l1_ssim_loss(image, gt, width, height, lambda_dssim, scratch, loss3, dL_dimage, s) != 0)
+        return fail(BGR_ERR_INVALID_ARG, "loss: NULL pointer or empty image");
+    return stage_check(false, s, "l1 + ssim loss");
+}
+
+BGR_API int bgr_adam_step(int n_groups, float* const* params, const float* const* grads, float* const* exp_avg,
+                          float* const* exp_avg_sq, const size_t* numel, const double* lr, double beta1,
+                          double beta2, double eps, int step, void* stream_v)
+{
+    cudaStream_t s = static_cast<cudaStream_t>(stream_v);
+    if (params == nullptr || grads == nullptr || exp_avg == nullptr || exp_avg_sq == nullptr || numel == nullptr ||
+        lr == nullptr ||
+        bgr::launch_adam(n_groups, params, grads, exp_avg, exp_avg_sq, numel, lr, beta1, beta2, eps, step, s) != 0)
+        return fail(BGR_ERR_INVALID_ARG, "adam: 1..8 groups with non-NULL arrays and step >= 1");
+    return stage_check(false, s, "adam step");
+}
+
 BGR_API int bgr_mark_visible(int P, const float* means3D, const float* viewmatrix,
                      const float* /*projmatrix*/, uint8_t* present, void* stream_v)
 {

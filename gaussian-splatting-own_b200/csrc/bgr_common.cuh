@@ -229,4 +229,13 @@ void launch_sh_grad_from_factors(int P, int begin, int end, int D, int M, int wo
                                  const float* means3D, const float* campos_all,
                                  const float* factors_all, float* dL_dsh, cudaStream_t s);
 
+
+// ---- the step after the path (train_step.cu) ------------------------------
+size_t loss_scratch_bytes(int W, int H);
+int launch_l1_ssim_loss(const float* image, const float* gt, int W, int H, float lambda, void* scratch,
+                        float* loss3, float* dL_dimage, cudaStream_t s);
+int launch_adam(int count, float* const* params, const float* const* grads, float* const* exp_avg,
+                float* const* exp_avg_sq, const size_t* numel, const double* lr, double beta1, double beta2,
+                double eps, int step, cudaStream_t s);
+
 }  // namespace bgr

@@ -86,6 +86,15 @@ def lib() -> C.CDLL:
                                   C.c_void_p, _ALLOC_FN, C.c_void_p, C.c_void_p, C.POINTER(C.c_int)]
     L.bgr_backward_raw.restype = C.c_int
     L.bgr_backward_raw.argtypes = [C.POINTER(_BackwardArgs), C.c_void_p, C.c_void_p, C.c_void_p]
+    L.bgr_loss_scratch_bytes.restype = C.c_size_t
+    L.bgr_loss_scratch_bytes.argtypes = [C.c_int, C.c_int]
+    L.bgr_l1_ssim_loss.restype = C.c_int
+    L.bgr_l1_ssim_loss.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p,
+                                   C.c_void_p, C.c_void_p]
+    L.bgr_adam_step.restype = C.c_int
+    L.bgr_adam_step.argtypes = [C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                C.POINTER(C.c_void_p), C.POINTER(C.c_size_t), C.POINTER(C.c_double), C.c_double,
+                                C.c_double, C.c_double, C.c_int, C.c_void_p]
     L.bgr_mark_visible.restype = C.c_int
     L.bgr_mark_visible.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                    C.c_void_p]
@@ -438,6 +447,45 @@ def rasterize_gaussians_raw_backward(background, xyz, radii, scaling_raw, rotati
                 dL_dscale=_ptr(dL_dscaling), dL_drot=_ptr(dL_drotation), debug=int(bool(debug)))
             _check(L.bgr_backward_raw(C.byref(a), _ptr(rest_), _ptr(dL_drest), _stream(dev)))
     return dL_dmeans2D, dL_dopacity, dL_dxyz, dL_ddc, dL_drest, dL_dscaling, dL_drotation
+
+
+# ---- the step after the path ------------------------------------------------
+def l1_ssim_loss(image, gt, lambda_dssim, need_grad=True):
+    """-> (loss3, dL_dimage): loss3 = device tensor {loss, l1, ssim} of train.py:91-92's loss
+    (utils/loss_utils.py:16-63), dL_dimage = d loss / d image (3,H,W) or None."""
+    if not image.is_cuda or image.dim() != 3 or image.size(0) != 3 or gt.shape != image.shape:
+        raise RuntimeError("l1_ssim_loss needs two CUDA tensors of shape (3, H, W)")
+    L = lib()
+    dev = image.device
+    H, W = int(image.size(1)), int(image.size(2))
+    with _on_device(dev):
+        img_, gt_ = _f32c(image, dev), _f32c(gt, dev)
+        scratch = torch.empty((L.bgr_loss_scratch_bytes(W, H),), dtype=torch.uint8, device=dev)
+        loss3 = torch.empty((3,), dtype=torch.float32, device=dev)
+        grad = torch.empty_like(img_) if need_grad else None
+        _check(L.bgr_l1_ssim_loss(img_.data_ptr(), gt_.data_ptr(), W, H, float(lambda_dssim), scratch.data_ptr(),
+                                  loss3.data_ptr(), grad.data_ptr() if need_grad else None, _stream(dev)))
+    return loss3, grad
+
+
+def adam_step(params, grads, exp_avgs, exp_avg_sqs, lrs, beta1, beta2, eps, step):
+    """torch.optim.Adam's update of up to eight parameter groups (one contiguous f32 CUDA tensor each,
+    one learning rate each) in one kernel launch; `step` is the 1-based update count."""
+    n = len(params)
+    if not (1 <= n <= 8) or not (len(grads) == len(exp_avgs) == len(exp_avg_sqs) == len(lrs) == n):
+        raise RuntimeError("adam_step takes 1..8 groups with one gradient, two moments and one lr each")
+    dev = params[0].device
+    for group in (params, grads, exp_avgs, exp_avg_sqs):
+        for t, p_ in zip(group, params):
+            if not t.is_cuda or t.device != dev or t.dtype != torch.float32 or not t.is_contiguous() \
+                    or t.numel() != p_.numel():
+                raise RuntimeError("adam_step needs contiguous float32 CUDA tensors of matching sizes on one device")
+    arr = lambda ts: (C.c_void_p * n)(*[t.data_ptr() for t in ts])  # noqa: E731
+    numel = (C.c_size_t * n)(*[p_.numel() for p_ in params])
+    lr = (C.c_double * n)(*[float(x) for x in lrs])
+    with _on_device(dev):
+        _check(lib().bgr_adam_step(n, arr(params), arr(grads), arr(exp_avgs), arr(exp_avg_sqs), numel, lr,
+                                   float(beta1), float(beta2), float(eps), int(step), _stream(dev)))
 
 
 def mark_visible(means3D, viewmatrix, projmatrix):

@@ -162,6 +162,25 @@ BGR_API int bgr_forward_raw(const BgrForwardArgs* args, const float* features_re
 BGR_API int bgr_backward_raw(const BgrBackwardArgs* args, const float* features_rest,
                 float* dL_dfeatures_rest, void* stream);
 
+/* ---- the step after the path (new) ---------------------------------------
+ * The trainer's loss, train.py:91-92 with utils/loss_utils.py:16-63:
+ *     loss = (1 - lambda_dssim) * mean|image - gt| + lambda_dssim * (1 - ssim(image, gt))
+ * (11x11 Gaussian window, sigma 1.5, zero padding, C1 = 0.01^2, C2 = 0.03^2, mean over 3 H W) and
+ * its gradient w.r.t. the rendered image, in three launches instead of PyTorch's ~50:
+ * image, gt: [3,H,W]. scratch: bgr_loss_scratch_bytes(W,H) bytes. loss3 (device): {loss, l1, ssim}.
+ * dL_dimage: [3,H,W] = d loss / d image (pass NULL to skip the backward kernel). */
+BGR_API size_t bgr_loss_scratch_bytes(int width, int height);
+BGR_API int bgr_l1_ssim_loss(const float* image, const float* gt, int width, int height,
+                             float lambda_dssim, void* scratch, float* loss3, float* dL_dimage,
+                             void* stream);
+/* torch.optim.Adam's update (scene/gaussian_model.py:149-160: six parameter groups, one learning
+ * rate each, eps 1e-15) for up to 8 groups in ONE launch. step is the 1-based update count. The
+ * hyper-parameters are doubles, as in torch: 1 - beta, the bias corrections and lr / (1 - beta1^t)
+ * are formed in double on the host and rounded to float32 once. */
+BGR_API int bgr_adam_step(int n_groups, float* const* params, const float* const* grads,
+                          float* const* exp_avg, float* const* exp_avg_sq, const size_t* numel,
+                          const double* lr, double beta1, double beta2, double eps, int step, void* stream);
+
 /* present[i] = 1 iff Gaussian i passes the near-plane test (auxiliary.h:139-164). */
 BGR_API int bgr_mark_visible(int P, const float* means3D, const float* viewmatrix,
                      const float* projmatrix, uint8_t* present, void* stream);
