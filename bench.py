@@ -641,6 +641,31 @@ def run_train(args, device):
     if "reference_ms" in out:
         out["speedup_vs_reference"] = round(out["reference_ms"] / out["fused_ms"], 3)
     out["speedup_vs_drop_in"] = round(out["drop_in_ms"] / out["fused_ms"], 3)
+
+    # the two f2 pieces on their own: loss forward + backward on a fixed image, one optimizer step
+    img0 = (gt + 0.1 * torch.randn_like(gt)).clamp(0, 1)
+
+    def loss_fused():
+        x = img0.detach().requires_grad_(True)
+        train_step.l1_ssim_loss(x, gt, 0.2).backward()
+
+    def loss_torch():
+        x = img0.detach().requires_grad_(True)
+        torch_loss(x).backward()
+
+    def adam_pair(fused):
+        P_ = {k: torch.nn.Parameter(v.clone()) for k, v in raw0.items()}
+        for t in P_.values():
+            t.grad = torch.randn_like(t) * 1e-3
+        groups = [{"params": [P_[k]], "lr": lrs[k], "name": k} for k in raw0]
+        opt = train_step.FusedAdam(groups, lr=0.0, eps=1e-15) if fused else torch.optim.Adam(groups, lr=0.0, eps=1e-15)
+        return opt.step
+    pieces = {}
+    for name, fn in (("loss_fused_ms", loss_fused), ("loss_torch_ms", loss_torch),
+                     ("adam_fused_ms", adam_pair(True)), ("adam_torch_ms", adam_pair(False))):
+        pieces[name] = round(timed(fn, args.steps, args.warmup, 1, device) / args.steps, 4)
+        torch.cuda.empty_cache()
+    out["pieces"] = pieces
     print(json.dumps(out))
 
 

@@ -154,6 +154,11 @@ def test_cuda_adam_large_groups_and_missing_gradients():
     init = {k: torch.randn(*s, generator=g, device="cuda") for k, s in shapes.items()}
     pa = {k: torch.nn.Parameter(v.clone()) for k, v in init.items()}
     pb = {k: torch.nn.Parameter(v.clone()) for k, v in init.items()}
+    # one group at a 4-byte offset: the kernel's 128-bit path must step aside for it
+    shifted = torch.empty(init["scaling"].numel() + 1, device="cuda")
+    shifted[1:] = init["scaling"].reshape(-1)
+    pb["scaling"] = torch.nn.Parameter(shifted[1:].view(P, 3))
+    assert pb["scaling"].data_ptr() % 16 != 0 and pb["scaling"].is_contiguous()
     oa = torch.optim.Adam([{"params": [pa[k]], "lr": LRS[k], "name": k} for k in GROUPS], lr=0.0, eps=1e-15)
     ob = train_step.FusedAdam([{"params": [pb[k]], "lr": LRS[k], "name": k} for k in GROUPS], lr=0.0, eps=1e-15)
     for step in range(3):
