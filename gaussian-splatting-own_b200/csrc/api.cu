@@ -440,6 +440,15 @@ BGR_API int bgr_l1_ssim_loss(const float* image, const float* gt, int width, int
     return stage_check(false, s, "l1 + ssim loss");
 }
 
+BGR_API int bgr_densification_stats(int P, const int* radii, const float* dL_dmean2D, float* max_radii2D,
+                                    float* xyz_gradient_accum, float* denom, void* stream_v)
+{
+    cudaStream_t s = static_cast<cudaStream_t>(stream_v);
+    if (bgr::launch_densification_stats(P, radii, dL_dmean2D, max_radii2D, xyz_gradient_accum, denom, s) != 0)
+        return fail(BGR_ERR_INVALID_ARG, "densification stats: P < 0 or NULL array");
+    return stage_check(false, s, "densification stats");
+}
+
 BGR_API int bgr_adam_step(int n_groups, float* const* params, const float* const* grads, float* const* exp_avg,
                           float* const* exp_avg_sq, const size_t* numel, const double* lr, double beta1,
                           double beta2, double eps, int step, void* stream_v)

@@ -234,6 +234,8 @@ void launch_sh_grad_from_factors(int P, int begin, int end, int D, int M, int wo
 size_t loss_scratch_bytes(int W, int H);
 int launch_l1_ssim_loss(const float* image, const float* gt, int W, int H, float lambda, void* scratch,
                         float* loss3, float* dL_dimage, cudaStream_t s);
+int launch_densification_stats(int P, const int* radii, const float* dL_dmean2D, float* max_radii2D,
+                               float* grad_accum, float* denom, cudaStream_t s);
 int launch_adam(int count, float* const* params, const float* const* grads, float* const* exp_avg,
                 float* const* exp_avg_sq, const size_t* numel, const double* lr, double beta1, double beta2,
                 double eps, int step, cudaStream_t s);

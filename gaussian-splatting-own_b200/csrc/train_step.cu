@@ -254,6 +254,24 @@ __global__ void __launch_bounds__(256) adam_kernel(AdamLaunch a)
     }
 }
 
+// Densification statistics of one view (train.py:114-116, scene/gaussian_model.py:405-407), one
+// pass instead of a boolean-mask gather / scatter chain: for Gaussians with radii > 0
+//   max_radii2D = max(max_radii2D, radii); xyz_gradient_accum += |dL/dmean2D.xy|; denom += 1
+__global__ void __launch_bounds__(256)
+densification_stats_kernel(int P, const int* __restrict__ radii, const float* __restrict__ dL_dmean2D,
+                           float* __restrict__ max_radii2D, float* __restrict__ grad_accum,
+                           float* __restrict__ denom)
+{
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= P) return;
+    const int r = radii[i];
+    if (r <= 0) return;
+    const float gx = dL_dmean2D[3 * (size_t)i], gy = dL_dmean2D[3 * (size_t)i + 1];
+    max_radii2D[i] = fmaxf(max_radii2D[i], (float)r);
+    grad_accum[i] += sqrtf(gx * gx + gy * gy);
+    denom[i] += 1.0f;
+}
+
 Window make_window()
 {
     // utils/loss_utils.py:23-25: exp(-(x - 5)^2 / (2 * 1.5^2)) in double, stored as float32,
@@ -301,6 +319,18 @@ int launch_l1_ssim_loss(const float* image, const float* gt, int W, int H, float
         ssim_backward_kernel<<<grid, LTHREADS, 0, s>>>(image, gt, W, H, win, maps, -lambda * inv_count,
                                                       (1.0f - lambda) * inv_count, dL_dimage);
     }
+    return 0;
+}
+
+int launch_densification_stats(int P, const int* radii, const float* dL_dmean2D, float* max_radii2D,
+                               float* grad_accum, float* denom, cudaStream_t s)
+{
+    if (P < 0 || (P > 0 && (radii == nullptr || dL_dmean2D == nullptr || max_radii2D == nullptr ||
+                            grad_accum == nullptr || denom == nullptr)))
+        return -1;
+    if (P == 0) return 0;
+    ++g_kernel_launches;
+    densification_stats_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, radii, dL_dmean2D, max_radii2D, grad_accum, denom);
     return 0;
 }
 

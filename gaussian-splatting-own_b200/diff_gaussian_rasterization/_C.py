@@ -91,6 +91,8 @@ def lib() -> C.CDLL:
     L.bgr_l1_ssim_loss.restype = C.c_int
     L.bgr_l1_ssim_loss.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p,
                                    C.c_void_p, C.c_void_p]
+    L.bgr_densification_stats.restype = C.c_int
+    L.bgr_densification_stats.argtypes = [C.c_int] + [C.c_void_p] * 6
     L.bgr_adam_step.restype = C.c_int
     L.bgr_adam_step.argtypes = [C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
                                 C.POINTER(C.c_void_p), C.POINTER(C.c_size_t), C.POINTER(C.c_double), C.c_double,
@@ -466,6 +468,24 @@ def l1_ssim_loss(image, gt, lambda_dssim, need_grad=True):
         _check(L.bgr_l1_ssim_loss(img_.data_ptr(), gt_.data_ptr(), W, H, float(lambda_dssim), scratch.data_ptr(),
                                   loss3.data_ptr(), grad.data_ptr() if need_grad else None, _stream(dev)))
     return loss3, grad
+
+
+def densification_stats(radii, dL_dmeans2D, max_radii2D, xyz_gradient_accum, denom):
+    """train.py:114-116 + scene/gaussian_model.py:405-407 for one view, in place, in one kernel."""
+    P = int(radii.numel())
+    dev = radii.device
+    ok = radii.is_cuda and radii.dtype == torch.int32 and radii.is_contiguous() and \
+        dL_dmeans2D.shape == (P, 3) and dL_dmeans2D.dtype == torch.float32 and dL_dmeans2D.is_contiguous()
+    for t in (dL_dmeans2D, max_radii2D, xyz_gradient_accum, denom):
+        ok = ok and t.is_cuda and t.device == dev
+    for t in (max_radii2D, xyz_gradient_accum, denom):
+        ok = ok and t.numel() == P and t.dtype == torch.float32 and t.is_contiguous()
+    if not ok:
+        raise RuntimeError("densification_stats needs contiguous CUDA tensors: radii int32 [P], dL_dmeans2D f32 "
+                           "[P,3], three f32 accumulators of P elements")
+    with _on_device(dev):
+        _check(lib().bgr_densification_stats(P, radii.data_ptr(), dL_dmeans2D.data_ptr(), max_radii2D.data_ptr(),
+                                             xyz_gradient_accum.data_ptr(), denom.data_ptr(), _stream(dev)))
 
 
 def adam_step(params, grads, exp_avgs, exp_avg_sqs, lrs, beta1, beta2, eps, step):

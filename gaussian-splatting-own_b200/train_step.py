@@ -47,6 +47,15 @@ def loss_terms(image: torch.Tensor, gt: torch.Tensor, lambda_dssim: float = 0.2)
     return _C.l1_ssim_loss(image.detach(), gt, lambda_dssim, need_grad=False)[0]
 
 
+@torch.no_grad()
+def densification_stats(radii, viewspace_grad, max_radii2D, xyz_gradient_accum, denom) -> None:
+    """The per-iteration bookkeeping of train.py:114-116, in place:
+    `max_radii2D[vis] = max(max_radii2D[vis], radii[vis])` and `add_densification_stats`
+    (scene/gaussian_model.py:405-407) with `vis = radii > 0`; `viewspace_grad` is the (P,3)
+    gradient the rasterizer leaves on `means2D`."""
+    _C.densification_stats(radii, viewspace_grad, max_radii2D, xyz_gradient_accum, denom)
+
+
 class FusedAdam:
     """torch.optim.Adam(param_groups, lr, betas, eps) with one tensor per group, one launch per step."""
 

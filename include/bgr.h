@@ -173,6 +173,13 @@ BGR_API size_t bgr_loss_scratch_bytes(int width, int height);
 BGR_API int bgr_l1_ssim_loss(const float* image, const float* gt, int width, int height,
                              float lambda_dssim, void* scratch, float* loss3, float* dL_dimage,
                              void* stream);
+/* (row f3) Densification statistics of one view, train.py:114-116 + scene/gaussian_model.py:405-407,
+ * in one pass: for every Gaussian with radii > 0
+ *     max_radii2D = max(max_radii2D, radii);  xyz_gradient_accum += |dL_dmean2D[:, :2]|;  denom += 1
+ * radii: [P] int32 and dL_dmean2D: [P,3] as bgr_forward / bgr_backward return them; the three
+ * accumulators are [P] (or [P,1]) float32, updated in place. */
+BGR_API int bgr_densification_stats(int P, const int* radii, const float* dL_dmean2D, float* max_radii2D,
+                                    float* xyz_gradient_accum, float* denom, void* stream);
 /* torch.optim.Adam's update (scene/gaussian_model.py:149-160: six parameter groups, one learning
  * rate each, eps 1e-15) for up to 8 groups in ONE launch. step is the 1-based update count. The
  * hyper-parameters are doubles, as in torch: 1 - beta, the bias corrections and lr / (1 - beta1^t)

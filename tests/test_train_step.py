@@ -173,3 +173,29 @@ def test_cuda_adam_large_groups_and_missing_gradients():
     for k in GROUPS:
         assert close(pb[k].detach(), pa[k].detach()), k
     assert ob.state[pb["opacity"]]["step"] == 2 and ob.state[pb["xyz"]]["step"] == 3
+
+
+@pytest.mark.gpu
+def test_cuda_densification_stats_match_the_trainer_bookkeeping():
+    """train.py:114-116 + scene/gaussian_model.py:405-407, restated with torch's masked ops."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import train_step
+    P = 100_003
+    g = torch.Generator(device="cuda").manual_seed(11)
+    radii = (torch.randint(-2, 40, (P,), generator=g, device="cuda").clamp_min(0)).int()
+    grad = torch.randn(P, 3, generator=g, device="cuda") * 1e-3
+    mr = torch.rand(P, generator=g, device="cuda") * 30
+    acc = torch.rand(P, 1, generator=g, device="cuda")
+    den = torch.randint(0, 5, (P, 1), generator=g, device="cuda").float()
+    w_mr, w_acc, w_den = mr.clone(), acc.clone(), den.clone()
+    vis = radii > 0
+    w_mr[vis] = torch.max(w_mr[vis], radii[vis])
+    w_acc[vis] += torch.norm(grad[vis, :2], dim=-1, keepdim=True)
+    w_den[vis] += 1
+    train_step.densification_stats(radii, grad, mr, acc, den)
+    assert torch.equal(mr, w_mr) and torch.equal(den, w_den)
+    assert torch.allclose(acc, w_acc, rtol=1e-6, atol=1e-9)
+    assert 0 < int(vis.sum()) < P
+    with pytest.raises(RuntimeError, match="densification_stats needs"):
+        train_step.densification_stats(radii.long(), grad, mr, acc, den)
