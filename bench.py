@@ -340,7 +340,7 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)", 1965.0
 
 
-NCU_RAW = "profiles/r2_e_ncu_full_raw.csv"
+NCU_RAW = "profiles/r2_g_ncu_full_raw.csv"
 _STAGE_KERNEL = {"render_backward": "render_backward_kernel", "render_forward": "render_forward_kernel",
                  "preprocess_backward": "preprocess_backward_kernel", "preprocess": "preprocess_kernel",
                  "scatter_keys": "scatter_keys_kernel", "tile_sort": "tile_sort_kernel"}
