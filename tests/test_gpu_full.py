@@ -112,7 +112,10 @@ def compare_with_reference(C_, sc, cam, bg, deg=3, mod=1.0, bad_frac=1e-3, color
         spread, _ = violations(r2, r)
         mine, _ = violations(n, r)
         assert torch.isfinite(n).all(), k
-        assert mine <= max(3 * spread, 2e-5), f"{k}: {mine:.2e} of elements off vs reference spread {spread:.2e}"
+        # floor: 2e-5 of the elements, and never fewer than five (on a 20K-Gaussian scene 2e-5 of
+        # dL_dcov3D is 2.4 elements, inside the run-to-run noise of the accumulation order)
+        floor = max(2e-5, 5.0 / max(r.numel(), 1))
+        assert mine <= max(3 * spread, floor), f"{k}: {mine:.2e} of elements off vs reference spread {spread:.2e}"
         # worst element against the tensor's magnitude: 1e-3, or 3x what two runs of the reference
         # differ by on their worst element (cancelling terms amplify the atomics' order noise)
         ref_norm_err = ((r2.double() - r.double()).abs().max() / r.double().abs().max().clamp_min(1e-30)).item() if r.numel() else 0.0
