@@ -14,7 +14,7 @@ from pathlib import Path
 HERE = Path(__file__).resolve().parent
 CSRC = HERE / "csrc"
 OUT = HERE / "diff_gaussian_rasterization" / "libbgr.so"
-SOURCES = ["api.cu", "preprocess.cu", "binning.cu", "radix_sort.cu", "render_fwd.cu",
+SOURCES = ["api.cu", "preprocess.cu", "binning.cu", "render_fwd.cu",
            "render_bwd.cu", "preprocess_bwd.cu", "nvls_allreduce.cu", "train_step.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",

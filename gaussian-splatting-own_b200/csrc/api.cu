@@ -556,39 +556,4 @@ BGR_API int bgr_sh_grad_from_factors(int P, int D, int M, int world, const float
                                           dL_dsh, stream_v);
 }
 
-BGR_API size_t bgr_sort_temp_bytes(size_t n) { return bgr::sort_temp_layout(n).total; }
-
-BGR_API int bgr_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, size_t n,
-                   int bit_lo, int bit_hi, void* temp, void* stream_v, int* result_in_b)
-{
-    cudaStream_t s = static_cast<cudaStream_t>(stream_v);
-    if (result_in_b == nullptr) return fail(BGR_ERR_INVALID_ARG, "null argument");
-    if (bit_lo < 0 || bit_hi > 64 || bit_hi < bit_lo) return fail(BGR_ERR_INVALID_ARG, "bad bit range");
-    if ((vals_a == nullptr) != (vals_b == nullptr))
-        return fail(BGR_ERR_INVALID_ARG, "give both value buffers or neither");
-    if (bgr::radix_sort(keys_a, keys_b, vals_a, vals_b, n, bit_lo, bit_hi, temp, s, result_in_b) != 0)
-        return fail(BGR_ERR_INVALID_ARG, "unsupported sort size or bit range");
-    return stage_check(false, s, "radix sort");
-}
-
-BGR_API size_t bgr_scan_temp_bytes(size_t n)
-{
-    return bgr::align_up(((n + bgr::SCAN_TILE - 1) / bgr::SCAN_TILE + 1) * 8 + 256, 256);
-}
-
-BGR_API int bgr_inclusive_scan_u32(const uint32_t* in, uint32_t* out, size_t n, void* temp, void* stream_v)
-{
-    cudaStream_t s = static_cast<cudaStream_t>(stream_v);
-    if (n == 0) return BGR_OK;
-    if (n >= (1ull << 32)) return fail(BGR_ERR_INVALID_ARG, "n too large");
-    const size_t bytes = bgr_scan_temp_bytes(n);
-    int rc = check_cuda(cudaMemsetAsync(temp, 0, bytes, s), "memset scan state");
-    if (rc) return rc;
-    // layout: [0,256) ticket, then the look-back state
-    uint32_t* ticket = static_cast<uint32_t*>(temp);
-    uint64_t* state = reinterpret_cast<uint64_t*>(static_cast<unsigned char*>(temp) + 256);
-    bgr::launch_inclusive_scan(in, out, n, state, ticket, nullptr, s);
-    return stage_check(false, s, "scan");
-}
-
 }  // extern "C"

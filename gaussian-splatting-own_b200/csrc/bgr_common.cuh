@@ -51,10 +51,6 @@ extern std::atomic<unsigned long long> g_kernel_launches;   // several host thre
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-constexpr int SCAN_THREADS = 256;
-constexpr int SCAN_ITEMS = 8;
-constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
-
 inline GeomLayout geom_layout(size_t P)
 {
     GeomLayout L;
@@ -83,40 +79,9 @@ inline ImageLayout image_layout(size_t W, size_t H)
     return L;
 }
 
-// ---------------------------------------------------------------------------------------------
-// Radix sort geometry
-// ---------------------------------------------------------------------------------------------
-constexpr int RADIX_BITS = 8;
-constexpr int RADIX = 1 << RADIX_BITS;
-constexpr int SORT_THREADS = 256;
-constexpr int SORT_ITEMS = 16;
-constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
-constexpr int SORT_MAX_PASSES = 8;
-
-struct SortTempLayout {
-    size_t hist;      // u32[SORT_MAX_PASSES][RADIX]   global digit histograms -> exclusive bases
-    size_t tickets;   // u32[SORT_MAX_PASSES]
-    size_t status;    // u32[SORT_MAX_PASSES][nblocks][RADIX] decoupled look-back state
-    size_t total;
-    size_t nblocks;
-};
-
-inline SortTempLayout sort_temp_layout(size_t n)
-{
-    SortTempLayout L;
-    L.nblocks = (n + SORT_TILE - 1) / SORT_TILE;
-    if (L.nblocks == 0) L.nblocks = 1;
-    size_t o = 0;
-    L.hist = o;    o = align_up(o + SORT_MAX_PASSES * RADIX * 4, 256);
-    L.tickets = o; o = align_up(o + SORT_MAX_PASSES * 4, 256);
-    L.status = o;  o = align_up(o + (size_t)SORT_MAX_PASSES * L.nblocks * RADIX * 4, 256);
-    L.total = o;
-    return L;
-}
-
 // Binning buffer: the sorted Gaussian-id list the render kernels read, the per-tile key buckets
-// the scatter fills, and (only when some tile list exceeds the shared-memory sort capacity) a
-// second key array the global-memory sort ping-pongs with.
+// the scatter fills, and the second key array the per-tile sort's general (global-memory) path
+// ping-pongs with.
 inline BinningLayout binning_layout(size_t R, bool with_alt = false)
 {
     BinningLayout L;
@@ -172,8 +137,6 @@ struct PreprocessParams {
 void launch_preprocess(const PreprocessParams& p, cudaStream_t s);
 void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, uint8_t* present,
                          cudaStream_t s);
-void launch_inclusive_scan(const uint32_t* in, uint32_t* out, size_t n, uint64_t* state,
-                           uint32_t* ticket, uint32_t* total_out, cudaStream_t s);
 int  launch_tile_scan(int grid_x, int grid_y, int* coverage_grid, uint2* ranges, uint32_t* cursor,
                       GeomControl* control, cudaStream_t s);
 void launch_scatter_keys(int P, const GaussRec* rec, const int* radii, int grid_x, int grid_y,
@@ -182,10 +145,6 @@ void launch_scatter_keys(int P, const GaussRec* rec, const int* radii, int grid_
 // keys_alt may be NULL when no tile exceeds it.
 int  launch_tile_sort(uint32_t num_tiles, const uint2* ranges, uint64_t* keys, uint64_t* keys_alt,
                       int nb_idx, uint32_t smem_keys, uint32_t* point_list, cudaStream_t s);
-int  radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b, size_t n,
-                int bit_lo, int bit_hi, void* temp, cudaStream_t s, int* result_in_b,
-                 int scattered_from_bit = -1);
-int  radix_sort_passes(int bit_lo, int bit_hi);
 
 void launch_render_forward(int W, int H, const uint2* ranges, const uint32_t* point_list,
                            const GaussRec* rec, const float* colors_precomp, const float* bg,

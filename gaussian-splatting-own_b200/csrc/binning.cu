@@ -28,112 +28,6 @@ namespace bgr {
 namespace {
 
 // --------------------------------------------------------------------------------------------
-// Single-pass inclusive scan with decoupled look-back.
-// state[b]: bits 63..32 = flag (0 = not ready, 1 = block aggregate, 2 = inclusive prefix),
-//           bits 31..0  = value. Block ids come from an atomic ticket so that a block only ever
-//           waits on blocks that have already started.
-// --------------------------------------------------------------------------------------------
-constexpr uint64_t FLAG_AGG = 1ull << 32;
-constexpr uint64_t FLAG_PREFIX = 2ull << 32;
-
-__device__ __forceinline__ uint64_t ld_volatile_u64(const uint64_t* p)
-{
-    return *reinterpret_cast<const volatile uint64_t*>(p);
-}
-__device__ __forceinline__ void st_volatile_u64(uint64_t* p, uint64_t v)
-{
-    *reinterpret_cast<volatile uint64_t*>(p) = v;
-}
-
-__global__ void __launch_bounds__(SCAN_THREADS)
-scan_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, size_t n, uint64_t* state,
-            uint32_t* ticket, uint32_t* total_out)
-{
-    __shared__ uint32_t s_bid;
-    __shared__ uint32_t s_warp[SCAN_THREADS / 32];
-    __shared__ uint32_t s_excl;
-
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) s_bid = atomicAdd(ticket, 1u);
-    __syncthreads();
-    const uint32_t bid = s_bid;
-    const size_t base = (size_t)bid * SCAN_TILE + (size_t)tid * SCAN_ITEMS;
-
-    uint32_t v[SCAN_ITEMS];
-    if (base + SCAN_ITEMS <= n && (reinterpret_cast<uintptr_t>(in) & 15) == 0) {
-        const uint4 a = *reinterpret_cast<const uint4*>(in + base);
-        const uint4 b = *reinterpret_cast<const uint4*>(in + base + 4);
-        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
-        v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
-    } else {
-#pragma unroll
-        for (int i = 0; i < SCAN_ITEMS; ++i) v[i] = (base + i < n) ? in[base + i] : 0u;
-    }
-    uint32_t tsum = 0;
-#pragma unroll
-    for (int i = 0; i < SCAN_ITEMS; ++i) { tsum += v[i]; v[i] = tsum; }  // thread-inclusive
-
-    // warp-inclusive scan of the thread totals
-    uint32_t incl = tsum;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
-        if (lane >= d) incl += t;
-    }
-    if (lane == 31) s_warp[warp] = incl;
-    __syncthreads();
-    uint32_t warp_off = 0, block_total = 0;
-#pragma unroll
-    for (int w = 0; w < SCAN_THREADS / 32; ++w) {
-        const uint32_t t = s_warp[w];
-        if (w < warp) warp_off += t;
-        block_total += t;
-    }
-    const uint32_t thread_excl = warp_off + incl - tsum;
-
-    if (warp == 0) {
-        if (lane == 0)
-            st_volatile_u64(&state[bid], (bid == 0 ? FLAG_PREFIX : FLAG_AGG) | block_total);
-        uint32_t excl = 0;
-        if (bid > 0) {
-            int pred = (int)bid - 1;
-            while (true) {
-                const int j = pred - lane;
-                uint64_t s = (j >= 0) ? ld_volatile_u64(&state[j]) : FLAG_PREFIX;
-                while (__any_sync(0xffffffffu, (s >> 32) == 0))
-                    s = (j >= 0) ? ld_volatile_u64(&state[j]) : FLAG_PREFIX;
-                const unsigned pmask = __ballot_sync(0xffffffffu, (s >> 32) == 2);
-                if (pmask) {
-                    const int first = __ffs(pmask) - 1;
-                    excl += __reduce_add_sync(0xffffffffu, lane <= first ? (uint32_t)s : 0u);
-                    break;
-                }
-                excl += __reduce_add_sync(0xffffffffu, (uint32_t)s);
-                pred -= 32;
-            }
-            if (lane == 0) st_volatile_u64(&state[bid], FLAG_PREFIX | (uint64_t)(excl + block_total));
-        }
-        if (lane == 0) {
-            s_excl = excl;
-            if ((size_t)(bid + 1) * SCAN_TILE >= n && total_out != nullptr)
-                *total_out = excl + block_total;
-        }
-    }
-    __syncthreads();
-    const uint32_t add = s_excl + thread_excl;
-    if (base + SCAN_ITEMS <= n && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
-        *reinterpret_cast<uint4*>(out + base) =
-            make_uint4(v[0] + add, v[1] + add, v[2] + add, v[3] + add);
-        *reinterpret_cast<uint4*>(out + base + 4) =
-            make_uint4(v[4] + add, v[5] + add, v[6] + add, v[7] + add);
-    } else {
-#pragma unroll
-        for (int i = 0; i < SCAN_ITEMS; ++i)
-            if (base + i < n) out[base + i] = v[i] + add;
-    }
-}
-
-// --------------------------------------------------------------------------------------------
 // Tile scan. grid is the (gx+1) x (gy+1) difference grid: the preprocess added +1 at
 // (min.x, min.y) and (max.x, max.y) and -1 at (max.x, min.y) and (min.x, max.y) of every visible
 // Gaussian's tile rectangle, so the inclusive 2-D prefix sum at (x, y) is the number of rectangles
@@ -650,15 +544,6 @@ int prepare_binning_kernels()
 }
 
 }  // namespace
-
-void launch_inclusive_scan(const uint32_t* in, uint32_t* out, size_t n, uint64_t* state,
-                           uint32_t* ticket, uint32_t* total_out, cudaStream_t s)
-{
-    if (n == 0) return;
-    const unsigned blocks = (unsigned)((n + SCAN_TILE - 1) / SCAN_TILE);
-    ++g_kernel_launches;
-    scan_kernel<<<blocks, SCAN_THREADS, 0, s>>>(in, out, n, state, ticket, total_out);
-}
 
 int launch_tile_scan(int grid_x, int grid_y, int* coverage_grid, uint2* ranges, uint32_t* cursor,
                      GeomControl* control, cudaStream_t s)

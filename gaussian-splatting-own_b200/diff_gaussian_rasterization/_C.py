@@ -103,15 +103,6 @@ def lib() -> C.CDLL:
     L.bgr_geom_layout.argtypes = [C.c_int, C.POINTER(C.c_size_t)]
     L.bgr_image_layout.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_size_t)]
     L.bgr_binning_layout.argtypes = [C.c_int, C.POINTER(C.c_size_t)]
-    L.bgr_sort_temp_bytes.restype = C.c_size_t
-    L.bgr_sort_temp_bytes.argtypes = [C.c_size_t]
-    L.bgr_radix_sort.restype = C.c_int
-    L.bgr_radix_sort.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
-                                 C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.POINTER(C.c_int)]
-    L.bgr_scan_temp_bytes.restype = C.c_size_t
-    L.bgr_scan_temp_bytes.argtypes = [C.c_size_t]
-    L.bgr_inclusive_scan_u32.restype = C.c_int
-    L.bgr_inclusive_scan_u32.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
     L.bgr_nvls_allreduce_f32.restype = C.c_int
     L.bgr_nvls_allreduce_f32.argtypes = [C.c_void_p, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int,
                                          C.c_void_p]
@@ -656,38 +647,3 @@ def binning_layout(R):
     o = (C.c_size_t * 3)()
     lib().bgr_binning_layout(int(R), o)
     return dict(zip(("point_list", "keys", "keys_alt"), [int(x) for x in o]))
-
-
-def radix_sort(keys: torch.Tensor, values: torch.Tensor | None, bit_lo: int, bit_hi: int):
-    """Stable sort of int64-viewed u64 keys (and optional int32-viewed u32 values) on key bits
-    [bit_lo, bit_hi). Returns (sorted_keys, sorted_values)."""
-    L = lib()
-    dev = keys.device
-    n = keys.numel()
-    with _on_device(dev):
-        ka = keys.contiguous().clone()
-        kb = torch.empty_like(ka)
-        va = values.contiguous().clone() if values is not None else None
-        vb = torch.empty_like(va) if va is not None else None
-        temp = torch.empty((L.bgr_sort_temp_bytes(n),), dtype=torch.uint8, device=dev)
-        in_b = C.c_int(0)
-        _check(L.bgr_radix_sort(ka.data_ptr(), kb.data_ptr(), va.data_ptr() if va is not None else None,
-                                vb.data_ptr() if vb is not None else None, n, bit_lo, bit_hi,
-                                temp.data_ptr(), _stream(dev), C.byref(in_b)))
-        torch.cuda.current_stream(dev).synchronize()
-    if in_b.value:
-        return kb, vb
-    return ka, va
-
-
-def inclusive_scan_u32(x: torch.Tensor) -> torch.Tensor:
-    L = lib()
-    dev = x.device
-    n = x.numel()
-    with _on_device(dev):
-        xin = x.contiguous()
-        out = torch.empty_like(xin)
-        temp = torch.empty((L.bgr_scan_temp_bytes(n),), dtype=torch.uint8, device=dev)
-        _check(L.bgr_inclusive_scan_u32(xin.data_ptr(), out.data_ptr(), n, temp.data_ptr(), _stream(dev)))
-        torch.cuda.current_stream(dev).synchronize()
-    return out

@@ -209,18 +209,6 @@ BGR_API void bgr_geom_layout(int P, size_t* offsets2);
 BGR_API void bgr_image_layout(int width, int height, size_t* offsets4);
 BGR_API void bgr_binning_layout(int R, size_t* offsets3);
 
-/* Sorting primitive on its own (used by tests and micro-benchmarks): stable LSD onesweep radix
- * sort of n u64 keys (optionally with u32 values) on key bits [bit_lo, bit_hi).
- * keys_a holds the input; the sorted result is returned in *keys_a or *keys_b as reported by
- * *result_in_b. temp must hold bgr_sort_temp_bytes(n) bytes. */
-BGR_API size_t bgr_sort_temp_bytes(size_t n);
-BGR_API int bgr_radix_sort(uint64_t* keys_a, uint64_t* keys_b, uint32_t* vals_a, uint32_t* vals_b,
-                   size_t n, int bit_lo, int bit_hi, void* temp, void* stream, int* result_in_b);
-
-/* Inclusive prefix sum of n u32 (tests). temp: bgr_scan_temp_bytes(n). */
-BGR_API size_t bgr_scan_temp_bytes(size_t n);
-BGR_API int bgr_inclusive_scan_u32(const uint32_t* in, uint32_t* out, size_t n, void* temp, void* stream);
-
 /* ---- view-parallel exchange (new; the reference has no multi-GPU path) ---------- */
 /* In-switch (NVLink multicast / NVLS) sum of floats [offset, offset+count) of a buffer that is
  * symmetrically mapped on `world` GPUs and bound to the multicast address `multicast_ptr`. Rank

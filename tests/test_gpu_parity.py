@@ -39,34 +39,6 @@ def to_cuda(scene):
 
 
 # ------------------------------------------------------------------------------------------------
-# primitives
-# ------------------------------------------------------------------------------------------------
-@pytest.mark.parametrize("n", [1, 7, 2048, 2049, 100_003, 3_000_001])
-def test_inclusive_scan(C_, n):
-    x = torch.randint(0, 50, (n,), dtype=torch.int32, device="cuda")
-    assert torch.equal(C_.inclusive_scan_u32(x), torch.cumsum(x.long(), 0).int())
-
-
-@pytest.mark.parametrize("n,lo,hi,pairs", [
-    (1, 0, 8, False), (1000, 0, 64, False), (4096, 3, 20, True), (4097, 22, 61, False),
-    (300_000, 0, 45, True), (3_500_000, 22, 61, False), (3_500_000, 0, 39, True),
-    (5_000_000, 10, 10, False), (0, 0, 32, True)])
-@pytest.mark.parametrize("ties", [False, True])
-def test_radix_sort_is_stable_on_bit_range(C_, n, lo, hi, pairs, ties):
-    g = torch.Generator(device="cuda").manual_seed(n + lo + hi)
-    keys = torch.randint(-2**63, 2**63 - 1, (n,), dtype=torch.int64, device="cuda", generator=g)
-    if ties and hi - lo > 6:
-        keys = keys & ~(((1 << (hi - lo - 6)) - 1) << lo)   # 64 distinct digits -> many ties
-    vals = torch.arange(n, dtype=torch.int32, device="cuda") if pairs else None
-    ks, vs = C_.radix_sort(keys, vals, lo, hi)
-    field = (keys ^ (-2**63)) if hi - lo == 64 else (keys >> lo) & ((1 << (hi - lo)) - 1)
-    order = torch.sort(field, stable=True).indices if hi > lo else torch.arange(n, device="cuda")
-    assert torch.equal(ks, keys[order])
-    if pairs:
-        assert torch.equal(vs, vals[order])
-
-
-# ------------------------------------------------------------------------------------------------
 # golden fixtures of the reference's CUDA code
 # ------------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("name", ["a", "b", "c"])
